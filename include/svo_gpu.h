@@ -1,0 +1,191 @@
+/*
+ * svo_gpu.h -- C ABI of the B200 (sm_100a) feature front-end: pyramid build, FAST-9/16, grid bucketing, pyramidal LK.
+ *
+ * This is the ONLY way host code reaches the CUDA kernels (libsvo_gpu.so: plain pointers and sizes, no C++ or torch
+ * types).  Each entry point names the reference interface (ikryukov/svo, paths relative to the reference tree) it stands
+ * in for.  There is no CPU fallback: every call either runs the sm_100a kernels or returns a negative SVO_GPU_E_* code.
+ *
+ * Conventions
+ *   - return value: 0 = ok, negative = error (svo_gpu_last_error(ctx) holds a message).
+ *   - host pointers are owned by the caller and never retained after the call returns; outputs are caller-allocated
+ *     with a stated capacity; a too-small capacity returns SVO_GPU_E_CAPACITY with the required count written,
+ *     never a silently truncated list.
+ *   - every call is synchronous (outputs valid on return), like the OpenCV calls the reference makes
+ *     (src/tracking.cpp:82, :101-105, :160-165 consume their results immediately).
+ *   - a context is bound to one device and is NOT thread-safe; use one context per host thread per device.
+ *   - "slot" = a persistent device-side image pyramid (0 <= slot < SVO_GPU_NUM_SLOTS); "lane" = one independent image
+ *     stream inside a batched call (0 <= lane < max_batch).  The single-image calls work on lane 0.
+ */
+#ifndef SVO_GPU_H
+#define SVO_GPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define SVO_GPU_API __declspec(dllexport)
+#else
+#define SVO_GPU_API __attribute__((visibility("default")))
+#endif
+
+#define SVO_GPU_OK 0
+#define SVO_GPU_E_ARG (-1)         /* bad argument (null pointer, size out of range, point outside the bucket table ...) */
+#define SVO_GPU_E_CAPACITY (-2)    /* output capacity too small; the required count has been written to *count_out */
+#define SVO_GPU_E_CUDA (-3)        /* a CUDA runtime call or kernel failed */
+#define SVO_GPU_E_UNSUPPORTED (-4) /* valid for OpenCV, not implemented here (OPTFLOW_USE_INITIAL_FLOW, window > 45) */
+#define SVO_GPU_E_STATE (-5)       /* slot not uploaded / pyramid not built (or built for a smaller window) */
+
+#define SVO_GPU_NUM_SLOTS 4
+#define SVO_GPU_MAX_LEVELS 8       /* pyramid levels 0..7 (OpenCV maxLevel <= 7) */
+#define SVO_GPU_MAX_WIN 45         /* largest LK window side */
+
+/* cv::TermCriteria::Type and cv::OPTFLOW_* flag values, so callers can pass OpenCV's constants straight through */
+#define SVO_GPU_TC_COUNT 1
+#define SVO_GPU_TC_EPS 2
+#define SVO_GPU_LK_USE_INITIAL_FLOW 4
+#define SVO_GPU_LK_GET_MIN_EIGENVALS 8
+
+/* memory kind of an image/points pointer handed to the *_batch / step calls */
+#define SVO_GPU_MEM_HOST 0
+#define SVO_GPU_MEM_DEVICE 1
+
+typedef struct svo_gpu_ctx svo_gpu_ctx;
+
+/* ---------------------------------------------------------------------------------------------- context ------- */
+
+/* Creates a context on CUDA device `device`: one stream, device buffers for SVO_GPU_NUM_SLOTS pyramids of up to
+ * max_w x max_h pixels and max_levels levels per lane, keypoint/track buffers of max_points entries per lane, and
+ * pinned staging.  Replaces nothing in the reference (which has no device); it is the state that
+ * Tracking::Tracking (src/tracking.cpp:22-59) would create next to mDetector. */
+SVO_GPU_API int svo_gpu_create(svo_gpu_ctx** out, int device, int max_w, int max_h, int max_levels, int max_points,
+                               int max_batch);
+SVO_GPU_API int svo_gpu_destroy(svo_gpu_ctx* ctx);
+/* message of the last failing call on this context ("" if none); with ctx == NULL, of the last failed create */
+SVO_GPU_API const char* svo_gpu_last_error(const svo_gpu_ctx* ctx);
+/* the cudaStream_t all work of this context is enqueued on (as void*), for callers that time with CUDA events */
+SVO_GPU_API void* svo_gpu_stream(svo_gpu_ctx* ctx);
+/* ABI version of this header */
+SVO_GPU_API int svo_gpu_abi_version(void);
+
+/* ---------------------------------------------------------------------------------------------- images -------- */
+
+/* Copies one 8-bit gray image (cv::Mat CV_8UC1: data, cols, rows, step) into `slot`, lane 0.
+ * Stands in for handing frame->leftImg()/rightImg() (include/frame.h:32-33) to an OpenCV call. */
+SVO_GPU_API int svo_gpu_upload(svo_gpu_ctx* ctx, int slot, const uint8_t* host, int w, int h, size_t stride_bytes);
+/* Same for `batch` images (lane b at images + b*image_stride_bytes); mem_kind says whether `images` is host or device. */
+SVO_GPU_API int svo_gpu_upload_batch(svo_gpu_ctx* ctx, int slot, const uint8_t* images, int mem_kind, int w, int h,
+                                     size_t stride_bytes, size_t image_stride_bytes, int batch);
+
+/* Builds the Gaussian pyramid of `slot` (all uploaded lanes): level l = pyrDown(level l-1), every level stored with a
+ * BORDER_REFLECT_101 margin.  Same result as cv::buildOpticalFlowPyramid(img, pyr, winSize, maxLevel, false), which
+ * cv::calcOpticalFlowPyrLK runs on both images on every call (src/tracking.cpp:101-105, :160-165); *levels_out gets the
+ * effective maxLevel (construction stops when a level would be <= winSize). */
+SVO_GPU_API int svo_gpu_build_pyramid(svo_gpu_ctx* ctx, int slot, int win_w, int win_h, int max_level, int* levels_out);
+/* Test/debug read-back of one pyramid level of lane `lane` (tightly packed w*h bytes). */
+SVO_GPU_API int svo_gpu_download_level(svo_gpu_ctx* ctx, int slot, int lane, int level, uint8_t* host, int capacity_bytes,
+                                       int* w_out, int* h_out);
+
+/* ---------------------------------------------------------------------------------------------- FAST ---------- */
+
+/* FAST-9/16 + optional 3x3 non-max suppression + optional pixel mask on level 0 of `slot`, lane 0; keypoints in raster
+ * order.  Replaces mDetector->detect(frame->leftImg(), keypoints, mask) (src/tracking.cpp:82) for the detector built by
+ * cv::FastFeatureDetector::create(threshold, nonMaxSuppression) (src/tracking.cpp:54-57).
+ *   mask_or_null: host CV_8UC1 mask of the image size (0 = reject), as built at src/tracking.cpp:76-79, or NULL.
+ *   xy_out[2*i], xy_out[2*i+1] = KeyPoint::pt; response_out[i] = KeyPoint::response (score with NMS, 0 without).
+ *   The other KeyPoint fields are constants: size 7, angle -1, octave 0, class_id -1. */
+SVO_GPU_API int svo_gpu_fast(svo_gpu_ctx* ctx, int slot, int threshold, int nms, const uint8_t* mask_or_null,
+                             size_t mask_stride, float* xy_out, float* response_out, int capacity, int* count_out);
+
+/* The reference's "do not re-detect near tracked features" mask, built on the device from the points themselves:
+ * 255 everywhere, 0 in the inclusive box [cvRound(x-half), cvRound(x+half)] x [cvRound(y-half), cvRound(y+half)]
+ * around each point (src/tracking.cpp:76-79, half = 10), then FAST as above.  Saves the w*h-byte mask upload. */
+SVO_GPU_API int svo_gpu_fast_masked_by_points(svo_gpu_ctx* ctx, int slot, int threshold, int nms, const float* mask_xy,
+                                              int n_mask_pts, float half, float* xy_out, float* response_out,
+                                              int capacity, int* count_out);
+
+/* ---------------------------------------------------------------------------------------------- bucketing ----- */
+
+/* FeatureSet::bucketingFeatures(image, bucket_size, features_per_bucket) (src/bucket.cpp:24-68, Bucket::add_feature
+ * :72-101, get_features :103-106), in place on (points, ages), bit-exact including its two quirks: a full bucket always
+ * overwrites its slot 0, and buckets aliased by the row stride are emitted twice.  img_w/img_h are image.cols/rows
+ * (src/bucket.cpp:29-30).  A point that maps outside the bucket table (undefined behaviour in the reference) returns
+ * SVO_GPU_E_ARG.  capacity = number of entries xy_inout/ages_inout can hold (>= n_in). */
+SVO_GPU_API int svo_gpu_bucket(svo_gpu_ctx* ctx, float* xy_inout, int* ages_inout, int n_in, int img_w, int img_h,
+                               int bucket_size, int per_bucket, int capacity, int* n_out);
+
+/* ---------------------------------------------------------------------------------------------- KLT ----------- */
+
+/* cv::calcOpticalFlowPyrLK(prevImg, nextImg, prevPts, nextPts, status, err, winSize, maxLevel, criteria, flags,
+ * minEigThreshold) on lane 0 of two slots whose pyramids were built with a window >= (win_w, win_h):
+ *   temporal tracking src/tracking.cpp:160-165 (21x21, maxLevel 3, {COUNT+EPS,50,0.001}, OPTFLOW_LK_GET_MIN_EIGENVALS)
+ *   stereo matching   src/tracking.cpp:101-105 (11x11, maxLevel 3, {COUNT+EPS,30,0.001}, flags 0).
+ * criteria_type/max_count/epsilon are cv::TermCriteria's fields; status is 0/1; err is the min-eigenvalue or the L1
+ * patch residual depending on flags.  OPTFLOW_USE_INITIAL_FLOW returns SVO_GPU_E_UNSUPPORTED (the reference never sets it). */
+SVO_GPU_API int svo_gpu_klt(svo_gpu_ctx* ctx, int slot_prev, int slot_next, const float* prev_xy, float* next_xy,
+                            uint8_t* status, float* err, int n, int win_w, int win_h, int max_level, int max_count,
+                            double epsilon, int criteria_type, int flags, double min_eig_threshold);
+/* total LK iterations executed by the last svo_gpu_klt / step call (all lanes), for the op model of the roofline */
+SVO_GPU_API long long svo_gpu_last_klt_iterations(svo_gpu_ctx* ctx);
+
+/* ---------------------------------------------------------------------------------------------- per-frame step - */
+
+/* Parameters of one front-end frame, i.e. what Tracking::startStereo does per key-frame (src/tracking.cpp:240-257):
+ * trackFrames(prev, curr) (:154-179) then extractFeatures(curr) (:74-92) with bucketing at the "todo" of :88. */
+typedef struct svo_gpu_step_params {
+    int w, h;               /* image size of every lane */
+    int fast_threshold;     /* include/config_reader.h:36 (20) */
+    int fast_nms;           /* include/config_reader.h:37 (true) */
+    float mask_half;        /* src/tracking.cpp:78 (10); <= 0 disables the tracked-points mask */
+    int bucket_size;        /* FeatureSet::bucketingFeatures argument */
+    int per_bucket;         /* FeatureSet::bucketingFeatures argument */
+    int max_tracks;         /* tracks carried to the next frame = first max_tracks bucketed features */
+    int win_w, win_h;       /* src/tracking.cpp:163 (21, 21) */
+    int max_level;          /* src/tracking.cpp:163 (3) */
+    int max_count;          /* src/tracking.cpp:157 (50) */
+    double epsilon;         /* src/tracking.cpp:157 (0.001) */
+    int criteria_type;      /* COUNT + EPS */
+    int flags;              /* src/tracking.cpp:164 (OPTFLOW_LK_GET_MIN_EIGENVALS) */
+    double min_eig_threshold; /* OpenCV default 1e-4 */
+} svo_gpu_step_params;
+
+/* Host-side views of one step's results; any pointer may be NULL (that output is then left on the device).
+ * Arrays are [batch][capacity] with the per-lane strides given in elements. */
+typedef struct svo_gpu_step_outputs {
+    int* n_tracked;         /* [batch] number of points LK was run on in this step (0 on the first step) */
+    float* next_xy;         /* [batch][track_capacity][2] */
+    uint8_t* status;        /* [batch][track_capacity] */
+    float* err;             /* [batch][track_capacity] */
+    int track_capacity;
+    int* n_keypoints;       /* [batch] FAST keypoints found on the new frame */
+    float* kp_xy;           /* [batch][kp_capacity][2] */
+    float* kp_response;     /* [batch][kp_capacity] */
+    int kp_capacity;
+    int* n_bucketed;        /* [batch] features kept by bucketing; the first max_tracks of them are the new tracks */
+    float* bucket_xy;       /* [batch][bucket_capacity][2] */
+    int bucket_capacity;
+} svo_gpu_step_outputs;
+
+/* One frame of `batch` independent streams: ingest images[b] (host or device memory), build its pyramid, run LK from
+ * each lane's previous frame on that lane's current tracks, run FAST (+ tracked-points mask) on the new frame, bucket
+ * the detections, and make the first max_tracks of them the lane's tracks for the next call.  The context ping-pongs
+ * two slots internally (SVO_GPU_NUM_SLOTS-2 and -1).  Lanes never interact; this is how independent sequences share one
+ * GPU (and, with one context per device, several GPUs). */
+SVO_GPU_API int svo_gpu_step(svo_gpu_ctx* ctx, const uint8_t* images, int mem_kind, size_t stride_bytes,
+                             size_t image_stride_bytes, int batch, const svo_gpu_step_params* params,
+                             const svo_gpu_step_outputs* outputs_or_null);
+/* Forgets the previous frame and tracks of every lane (start of a new set of sequences). */
+SVO_GPU_API int svo_gpu_step_reset(svo_gpu_ctx* ctx);
+/* Number of kernel launches (graph kernel nodes included) issued by this context so far. */
+SVO_GPU_API long long svo_gpu_launch_count(const svo_gpu_ctx* ctx);
+/* Per-stage device time of the last svo_gpu_step in milliseconds (CUDA events on the context stream):
+ * ms[0] ingest+pyramid, ms[1] LK, ms[2] FAST, ms[3] bucketing.  Only recorded when enabled (adds event overhead). */
+SVO_GPU_API int svo_gpu_step_profile(svo_gpu_ctx* ctx, int enable, float ms_out[4]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SVO_GPU_H */

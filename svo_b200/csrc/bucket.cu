@@ -1,0 +1,151 @@
+// bucket.cu -- K3: grid bucketing, bit-exact with the reference's FeatureSet::bucketingFeatures, quirks included.
+//
+// Reference: src/bucket.cpp:24-68 (bucketingFeatures), :72-101 (Bucket::add_feature), :103-106 (get_features),
+// include/bucket.h:21-50; restated in SURVEY.md Appendix B and oracle/svo_oracle.c:orc_bucket.
+//   Hc = rows / bs, Wc = cols / bs; (Hc+1)*(Wc+1) buckets addressed with stride Wc:  idx = int(y/bs)*Wc + int(x/bs)
+//   a bucket keeps its first k arrivals (input order); once full, EVERY later arrival overwrites slot 0
+//   (the age comparison at :91 tests the incoming age against itself), so a bucket that received m > k arrivals
+//   a_0..a_{m-1} ends as [a_{m-1}, a_1, ..., a_{k-1}]
+//   emission visits h in [0,Hc], w in [0,Wc] with idx = h*Wc + w, so aliased buckets are emitted twice.
+//
+// GPU formulation (order-independent, hence deterministic although it uses atomics):
+//   per bucket we need  m = number of arrivals, the k SMALLEST input indices, and the LARGEST input index.
+//   insert kernel: atomicAdd for m, atomicMax for the largest index, and a lock-free sorted insertion for the k
+//   smallest: walk the bucket's k slots with atomicMin, carrying the displaced (larger) value onwards.  Every slot only
+//   ever decreases and every atomicMin forwards the larger of (incoming, resident), so slot j ends up holding the
+//   (j+1)-th smallest index whatever the interleaving.  A plain read of the last slot lets late arrivals skip the walk.
+//   emit kernel: each CTA owns 256 consecutive entries of the emission sequence, recomputes the offset of its first
+//   entry by summing min(m, k) over all earlier entries (a few thousand L2 reads), scans its own, and gathers.
+#include <limits.h>
+
+#include "svo_internal.cuh"
+
+namespace svo {
+
+namespace {
+
+constexpr int kEmpty = 0x7f7f7f7f;   // cudaMemset(0x7f) pattern; larger than any input index
+
+__global__ void __launch_bounds__(256) bucket_insert_kernel(const float2* __restrict__ in_xy, size_t in_lane,
+                                                            const int* __restrict__ n_dev, int n_max, int Wc, int nb,
+                                                            int bs, int k, BucketBufs bb)
+{
+    const int lane_id = blockIdx.y;
+    const int n = min(n_dev[lane_id], n_max);
+    int* slots = bb.cell_slots + (size_t)lane_id * bb.slots_cap;
+    int* cnt = bb.cell_cnt + (size_t)lane_id * bb.cells_cap;
+    int* last = bb.cell_last + (size_t)lane_id * bb.cells_cap;
+    const float fbs = (float)bs;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float2 p = in_xy[(size_t)lane_id * in_lane + i];
+        const float fy = __fdiv_rn(p.y, fbs), fx = __fdiv_rn(p.x, fbs);   // float / int -> float, src/bucket.cpp:50-51
+        if (!(fabsf(fy) < 2.0e9f) || !(fabsf(fx) < 2.0e9f)) { bb.err_flag[lane_id] = 1; continue; }
+        const long long idx = (long long)(int)fy * Wc + (int)fx;           // truncation toward zero, stride Wc (:52)
+        if (idx < 0 || idx >= nb) { bb.err_flag[lane_id] = 1; continue; }   // out-of-bounds write in the reference (UB)
+        atomicAdd(cnt + idx, 1);
+        atomicMax(last + idx, i);
+        int* s = slots + idx * k;
+        if (*reinterpret_cast<volatile int*>(s + k - 1) < i) continue;     // k smaller indices are already in
+        int v = i;
+        for (int j = 0; j < k; ++j) {
+            const int old = atomicMin(s + j, v);
+            if (old == kEmpty) break;
+            if (old > v) v = old;
+        }
+    }
+}
+
+__device__ __forceinline__ int emit_count(const int* __restrict__ cnt, int e, int Wc, int k)
+{
+    const int hh = e / (Wc + 1), ww = e - hh * (Wc + 1);
+    return min(cnt[hh * Wc + ww], k);
+}
+
+__global__ void __launch_bounds__(256) bucket_emit_kernel(const float2* __restrict__ in_xy, const int* __restrict__ in_age,
+                                                          size_t in_lane, int Wc, int nemit, int k, BucketBufs bb)
+{
+    __shared__ int wsum[8];
+    __shared__ int sbase;
+    const int lane_id = blockIdx.y;
+    const int tid = threadIdx.x, warp = tid >> 5, ln = tid & 31;
+    const int* slots = bb.cell_slots + (size_t)lane_id * bb.slots_cap;
+    const int* cnt = bb.cell_cnt + (size_t)lane_id * bb.cells_cap;
+    const int* last = bb.cell_last + (size_t)lane_id * bb.cells_cap;
+    const int e0 = blockIdx.x * 256;
+
+    // offset of this CTA's first entry
+    int part = 0;
+    for (int e = tid; e < e0; e += 256) part += emit_count(cnt, e, Wc, k);
+#pragma unroll
+    for (int o = 16; o; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+    if (ln == 0) wsum[warp] = part;
+    __syncthreads();
+    if (tid == 0) {
+        int s = 0;
+        for (int i = 0; i < 8; ++i) s += wsum[i];
+        sbase = s;
+    }
+    __syncthreads();
+    const int base = sbase;
+    __syncthreads();
+
+    // exclusive scan of this CTA's 256 entries
+    const int e = e0 + tid;
+    int idx = 0, m = 0;
+    if (e < nemit) {
+        const int hh = e / (Wc + 1), ww = e - hh * (Wc + 1);
+        idx = hh * Wc + ww;
+        m = min(cnt[idx], k);
+    }
+    int inc = m;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, inc, o);
+        if (ln >= o) inc += v;
+    }
+    if (ln == 31) wsum[warp] = inc;
+    __syncthreads();
+    int woff = 0;
+    for (int i = 0; i < warp; ++i) woff += wsum[i];
+    const int off = base + woff + inc - m;
+
+    if (m > 0) {
+        const float2* ixy = in_xy + (size_t)lane_id * in_lane;
+        const int* iag = in_age ? in_age + (size_t)lane_id * in_lane : nullptr;
+        float2* oxy = bb.out_xy + (size_t)lane_id * bb.out_cap;
+        int* oag = bb.out_age + (size_t)lane_id * bb.out_cap;
+        const bool overflow = cnt[idx] > k;
+        for (int s = 0; s < m; ++s) {
+            const int src = (s == 0 && overflow) ? last[idx] : slots[(size_t)idx * k + s];
+            const int o = off + s;
+            if (o < bb.out_cap) {
+                oxy[o] = ixy[src];
+                oag[o] = iag ? iag[src] : 0;
+            }
+        }
+    }
+    if (e == nemit - 1) bb.out_count[lane_id] = off + m;   // required output length (may exceed out_cap)
+}
+
+}  // namespace
+
+void launch_bucket(cudaStream_t st, const float2* in_xy, const int* in_age, size_t in_lane, const int* n_dev, int n_max,
+                   int img_w, int img_h, int bucket_size, int per_bucket, const BucketBufs& bb, int batch,
+                   long long* launches)
+{
+    const int Hc = img_h / bucket_size, Wc = img_w / bucket_size;
+    const int nb = (Hc + 1) * (Wc + 1);
+    const int k = per_bucket;
+    // whole-batch clears (lanes are contiguous)
+    cudaMemsetAsync(bb.cell_slots, 0x7f, sizeof(int) * bb.slots_cap * batch, st);
+    cudaMemsetAsync(bb.cell_cnt, 0, sizeof(int) * bb.cells_cap * batch, st);
+    cudaMemsetAsync(bb.cell_last, 0xff, sizeof(int) * bb.cells_cap * batch, st);
+    cudaMemsetAsync(bb.err_flag, 0, sizeof(int) * batch, st);
+    int nblk = (n_max + 255) / 256;
+    nblk = nblk < 1 ? 1 : (nblk > 592 ? 592 : nblk);   // 148 SMs x 4
+    bucket_insert_kernel<<<dim3(nblk, batch), 256, 0, st>>>(in_xy, in_lane, n_dev, n_max, Wc, nb, bucket_size, k, bb);
+    bucket_emit_kernel<<<dim3((nb + 255) / 256, batch), 256, 0, st>>>(in_xy, in_age, in_lane, Wc, nb, k, bb);
+    if (launches) *launches += 2;
+}
+
+}  // namespace svo

@@ -1,0 +1,389 @@
+// capi.cu -- the C ABI of include/svo_gpu.h: context, device buffers, and the host side of every entry point.
+// No CPU implementation of any stage exists in this library: a call either enqueues the sm_100a kernels or fails.
+#include <limits.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <new>
+#include <vector>
+
+#include "svo_internal.cuh"
+
+using namespace svo;
+
+namespace {
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t bytes = 0;
+};
+
+struct Slot {
+    DevBuf raw_own;                 // context-owned copy of host uploads
+    const uint8_t* raw = nullptr;   // raw_own.p, or caller-owned device memory (mem_kind DEVICE: aliased, not copied)
+    size_t raw_pitch = 0, raw_lane = 0;
+    int w = 0, h = 0, batch = 0;
+    bool uploaded = false;
+    DevBuf pyr;
+    PyrGeom g{};
+    bool pyr_built = false;
+    int win_w = 0, win_h = 0;
+};
+
+thread_local char g_create_error[512] = "";
+
+}  // namespace
+
+struct svo_gpu_ctx {
+    int device = 0;
+    cudaStream_t st = nullptr;
+    int max_w = 0, max_h = 0, max_levels = 0, max_points = 0, max_batch = 0;
+    Slot slots[SVO_GPU_NUM_SLOTS];
+    char err[512] = "";
+    long long launches = 0;
+
+    // FAST
+    FastBufs fb{};
+    DevBuf mask;                  // [B][max_h * mask_pitch]
+    size_t mask_pitch = 0, mask_lane = 0;
+    // bucketing
+    BucketBufs bb{};
+    DevBuf cell_slots, cell_cnt, cell_last;
+    float2* bk_in_xy = nullptr;   // [B][max_points] staging for the host-pointer bucketing call
+    int* bk_in_age = nullptr;
+    // tracks / LK
+    float2* trk_xy = nullptr;     // [B][max_points] points LK starts from
+    float2* nxt_xy = nullptr;
+    uint8_t* trk_status = nullptr;
+    float* trk_err = nullptr;
+    int* trk_n = nullptr;         // [B]
+    int* int_max = nullptr;       // [B] all INT_MAX: "n is given by n_max" for the host-pointer calls
+    unsigned long long* d_iters = nullptr;
+    long long last_iters = 0;
+    // pinned scratch for small read-backs
+    int* h_small = nullptr;       // 4 * max_batch + 16 ints
+
+    // svo_gpu_step state
+    bool step_has_prev = false;
+    int step_cur = SVO_GPU_NUM_SLOTS - 2;
+    svo_gpu_step_params step_params{};
+    int step_batch = 0;
+    bool profile = false;
+    cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    float stage_ms[4] = {0, 0, 0, 0};
+};
+
+namespace {
+
+int fail(svo_gpu_ctx* c, int code, const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(c ? c->err : g_create_error, 512, fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define CK(call)                                                                                              \
+    do {                                                                                                      \
+        cudaError_t e_ = (call);                                                                              \
+        if (e_ != cudaSuccess)                                                                                \
+            return fail(ctx, SVO_GPU_E_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, \
+                        __LINE__);                                                                            \
+    } while (0)
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev)
+    {
+        cudaGetDevice(&prev);
+        if (prev != dev) cudaSetDevice(dev);
+        else prev = -1;
+    }
+    ~DeviceGuard()
+    {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// grow-only device buffer; growing synchronises the stream first so that no kernel still uses the old storage
+int ensure(svo_gpu_ctx* ctx, DevBuf& b, size_t bytes)
+{
+    if (bytes <= b.bytes) return 0;
+    CK(cudaStreamSynchronize(ctx->st));
+    if (b.p) CK(cudaFree(b.p));
+    b.p = nullptr;
+    b.bytes = 0;
+    CK(cudaMalloc(&b.p, bytes));
+    b.bytes = bytes;
+    return 0;
+}
+
+template <typename T>
+int dmalloc(svo_gpu_ctx* ctx, T*& p, size_t count)
+{
+    CK(cudaMalloc(reinterpret_cast<void**>(&p), sizeof(T) * (count ? count : 1)));
+    return 0;
+}
+
+// effective maxLevel of cv::buildOpticalFlowPyramid: stop when the next level would be <= winSize in a dimension
+int effective_levels(int w, int h, int win_w, int win_h, int max_level)
+{
+    for (int level = 0; level <= max_level; ++level) {
+        w = (w + 1) / 2;
+        h = (h + 1) / 2;
+        if (w <= win_w || h <= win_h) return level;
+    }
+    return max_level;
+}
+
+int margin_for(int win_w, int win_h) { return (int)round_up((size_t)std::max(win_w, win_h) + 9, 16); }
+
+void make_geometry(PyrGeom& g, int w, int h, int nlevels, int P)
+{
+    g.nlevels = nlevels;
+    g.P = P;
+    long long off = 0;
+    for (int l = 0; l < nlevels; ++l) {
+        LevelGeom& L = g.lv[l];
+        L.w = w;
+        L.h = h;
+        L.pitch = (int)round_up((size_t)w + 2 * P, 128);
+        L.pad_ = 0;
+        L.off = off + (long long)P * L.pitch + P;
+        off += (long long)L.pitch * (h + 2 * P);
+        off = (long long)round_up((size_t)off, 256);
+        w = (w + 1) / 2;
+        h = (h + 1) / 2;
+    }
+    g.lane_bytes = off;
+}
+
+int check_slot(svo_gpu_ctx* ctx, int slot)
+{
+    if (slot < 0 || slot >= SVO_GPU_NUM_SLOTS) return fail(ctx, SVO_GPU_E_ARG, "slot %d out of range", slot);
+    return 0;
+}
+
+}  // namespace
+
+// ================================================================================================ context
+extern "C" int svo_gpu_abi_version(void) { return 1; }
+
+extern "C" const char* svo_gpu_last_error(const svo_gpu_ctx* ctx) { return ctx ? ctx->err : g_create_error; }
+
+extern "C" void* svo_gpu_stream(svo_gpu_ctx* ctx) { return ctx ? (void*)ctx->st : nullptr; }
+
+extern "C" long long svo_gpu_launch_count(const svo_gpu_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+extern "C" long long svo_gpu_last_klt_iterations(svo_gpu_ctx* ctx) { return ctx ? ctx->last_iters : 0; }
+
+static int create_buffers(svo_gpu_ctx* ctx)
+{
+    const size_t B = (size_t)ctx->max_batch, NP = (size_t)ctx->max_points;
+    // FAST segments
+    FastBufs& fb = ctx->fb;
+    fb.rows_cap = ctx->max_h;
+    fb.ntx_cap = (ctx->max_w + kFastTW - 1) / kFastTW;
+    fb.kp_cap = ctx->max_points;
+    if (int r = dmalloc(ctx, fb.rowtotal, B * fb.rows_cap)) return r;
+    if (int r = dmalloc(ctx, fb.segcnt, B * fb.rows_cap * fb.ntx_cap)) return r;
+    if (int r = dmalloc(ctx, fb.segkp, B * fb.rows_cap * fb.ntx_cap * kFastTW)) return r;
+    if (int r = dmalloc(ctx, fb.kp_xy, B * NP)) return r;
+    if (int r = dmalloc(ctx, fb.kp_resp, B * NP)) return r;
+    if (int r = dmalloc(ctx, fb.kp_count, B)) return r;
+    // bucketing
+    BucketBufs& bb = ctx->bb;
+    bb.out_cap = ctx->max_points;
+    if (int r = dmalloc(ctx, bb.out_xy, B * NP)) return r;
+    if (int r = dmalloc(ctx, bb.out_age, B * NP)) return r;
+    if (int r = dmalloc(ctx, bb.out_count, B)) return r;
+    if (int r = dmalloc(ctx, bb.err_flag, B)) return r;
+    if (int r = dmalloc(ctx, ctx->bk_in_xy, B * NP)) return r;
+    if (int r = dmalloc(ctx, ctx->bk_in_age, B * NP)) return r;
+    // tracks
+    if (int r = dmalloc(ctx, ctx->trk_xy, B * NP)) return r;
+    if (int r = dmalloc(ctx, ctx->nxt_xy, B * NP)) return r;
+    if (int r = dmalloc(ctx, ctx->trk_status, B * NP)) return r;
+    if (int r = dmalloc(ctx, ctx->trk_err, B * NP)) return r;
+    if (int r = dmalloc(ctx, ctx->trk_n, B)) return r;
+    if (int r = dmalloc(ctx, ctx->int_max, B)) return r;
+    if (int r = dmalloc(ctx, ctx->d_iters, 1)) return r;
+    CK(cudaMemsetAsync(ctx->trk_n, 0, sizeof(int) * B, ctx->st));
+    CK(cudaMemsetAsync(ctx->d_iters, 0, sizeof(unsigned long long), ctx->st));
+    {
+        std::vector<int> big(B, INT_MAX);
+        CK(cudaMemcpy(ctx->int_max, big.data(), sizeof(int) * B, cudaMemcpyHostToDevice));
+    }
+    CK(cudaMallocHost(reinterpret_cast<void**>(&ctx->h_small), sizeof(int) * (4 * B + 16)));
+    for (auto& e : ctx->ev) CK(cudaEventCreate(&e));
+    CK(cudaStreamSynchronize(ctx->st));
+    return 0;
+}
+
+extern "C" int svo_gpu_create(svo_gpu_ctx** out, int device, int max_w, int max_h, int max_levels, int max_points,
+                              int max_batch)
+{
+    svo_gpu_ctx* ctx = nullptr;   // CK/fail write to g_create_error while ctx is null
+    if (!out) return fail(ctx, SVO_GPU_E_ARG, "out is null");
+    *out = nullptr;
+    if (max_w < 1 || max_h < 1 || max_w > 65536 || max_h > 65536 || max_levels < 1 || max_levels > SVO_GPU_MAX_LEVELS ||
+        max_points < 1 || max_batch < 1 || max_batch > 65535)
+        return fail(ctx, SVO_GPU_E_ARG, "svo_gpu_create: argument out of range");
+    int ndev = 0;
+    CK(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return fail(ctx, SVO_GPU_E_ARG, "device %d not present (%d devices)", device, ndev);
+    DeviceGuard guard(device);
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10)
+        return fail(ctx, SVO_GPU_E_UNSUPPORTED, "device %d is sm_%d%d; this library carries sm_100a code only", device,
+                    prop.major, prop.minor);
+    svo_gpu_ctx* c = new (std::nothrow) svo_gpu_ctx();
+    if (!c) return fail(ctx, SVO_GPU_E_ARG, "out of host memory");
+    c->device = device;
+    c->max_w = max_w; c->max_h = max_h; c->max_levels = max_levels; c->max_points = max_points; c->max_batch = max_batch;
+    cudaError_t e = cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking);
+    if (e != cudaSuccess) {
+        delete c;
+        return fail(ctx, SVO_GPU_E_CUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(e));
+    }
+    int r = create_buffers(c);
+    if (r) {
+        snprintf(g_create_error, sizeof g_create_error, "%s", c->err);
+        svo_gpu_destroy(c);
+        return r;
+    }
+    *out = c;
+    return 0;
+}
+
+extern "C" int svo_gpu_destroy(svo_gpu_ctx* ctx)
+{
+    if (!ctx) return 0;
+    DeviceGuard guard(ctx->device);
+    if (ctx->st) cudaStreamSynchronize(ctx->st);
+    for (auto& s : ctx->slots) {
+        cudaFree(s.raw_own.p);
+        cudaFree(s.pyr.p);
+    }
+    void* bufs[] = {ctx->fb.rowtotal, ctx->fb.segcnt, ctx->fb.segkp, ctx->fb.kp_xy, ctx->fb.kp_resp, ctx->fb.kp_count,
+                    ctx->mask.p, ctx->bb.out_xy, ctx->bb.out_age, ctx->bb.out_count, ctx->bb.err_flag, ctx->cell_slots.p,
+                    ctx->cell_cnt.p, ctx->cell_last.p, ctx->bk_in_xy, ctx->bk_in_age, ctx->trk_xy, ctx->nxt_xy,
+                    ctx->trk_status, ctx->trk_err, ctx->trk_n, ctx->int_max, ctx->d_iters};
+    for (void* p : bufs) cudaFree(p);
+    if (ctx->h_small) cudaFreeHost(ctx->h_small);
+    for (auto& e : ctx->ev)
+        if (e) cudaEventDestroy(e);
+    if (ctx->st) cudaStreamDestroy(ctx->st);
+    delete ctx;
+    return 0;
+}
+
+// ================================================================================================ images
+extern "C" int svo_gpu_upload_batch(svo_gpu_ctx* ctx, int slot, const uint8_t* images, int mem_kind, int w, int h,
+                                    size_t stride_bytes, size_t image_stride_bytes, int batch)
+{
+    if (!ctx) return SVO_GPU_E_ARG;
+    if (int r = check_slot(ctx, slot)) return r;
+    if (!images) return fail(ctx, SVO_GPU_E_ARG, "images is null");
+    if (w < 1 || h < 1 || w > ctx->max_w || h > ctx->max_h)
+        return fail(ctx, SVO_GPU_E_ARG, "image %dx%d outside the context's 1..%dx1..%d", w, h, ctx->max_w, ctx->max_h);
+    if (batch < 1 || batch > ctx->max_batch) return fail(ctx, SVO_GPU_E_ARG, "batch %d outside 1..%d", batch, ctx->max_batch);
+    if (stride_bytes < (size_t)w) return fail(ctx, SVO_GPU_E_ARG, "stride %zu < width %d", stride_bytes, w);
+    if (batch > 1 && image_stride_bytes < stride_bytes * (size_t)h)
+        return fail(ctx, SVO_GPU_E_ARG, "image stride smaller than one image");
+    DeviceGuard guard(ctx->device);
+    Slot& s = ctx->slots[slot];
+    if (mem_kind == SVO_GPU_MEM_DEVICE) {
+        s.raw = images;   // aliased: the caller keeps it alive until the consuming calls have returned
+        s.raw_pitch = stride_bytes;
+        s.raw_lane = image_stride_bytes;
+    } else if (mem_kind == SVO_GPU_MEM_HOST) {
+        const size_t pitch = round_up((size_t)w, 128);
+        const size_t lane = pitch * (size_t)h;
+        if (int r = ensure(ctx, s.raw_own, lane * (size_t)ctx->max_batch)) return r;
+        uint8_t* d = static_cast<uint8_t*>(s.raw_own.p);
+        if (stride_bytes == (size_t)w && pitch == (size_t)w) {
+            for (int b = 0; b < batch; ++b)
+                CK(cudaMemcpyAsync(d + b * lane, images + b * image_stride_bytes, lane, cudaMemcpyHostToDevice, ctx->st));
+        } else {
+            for (int b = 0; b < batch; ++b)
+                CK(cudaMemcpy2DAsync(d + b * lane, pitch, images + b * image_stride_bytes, stride_bytes, (size_t)w,
+                                     (size_t)h, cudaMemcpyHostToDevice, ctx->st));
+        }
+        s.raw = d;
+        s.raw_pitch = pitch;
+        s.raw_lane = lane;
+    } else {
+        return fail(ctx, SVO_GPU_E_ARG, "mem_kind %d unknown", mem_kind);
+    }
+    s.w = w; s.h = h; s.batch = batch;
+    s.uploaded = true;
+    s.pyr_built = false;
+    return 0;
+}
+
+extern "C" int svo_gpu_upload(svo_gpu_ctx* ctx, int slot, const uint8_t* host, int w, int h, size_t stride_bytes)
+{
+    return svo_gpu_upload_batch(ctx, slot, host, SVO_GPU_MEM_HOST, w, h, stride_bytes, stride_bytes * (size_t)(h > 0 ? h : 0), 1);
+}
+
+// enqueue only (no synchronisation): ingest + pyrDown chain of every lane of the slot
+static int enqueue_pyramid(svo_gpu_ctx* ctx, Slot& s, int win_w, int win_h, int max_level, int* levels_out)
+{
+    if (!s.uploaded) return fail(ctx, SVO_GPU_E_STATE, "slot has no image");
+    if (win_w <= 2 || win_h <= 2 || win_w > SVO_GPU_MAX_WIN || win_h > SVO_GPU_MAX_WIN)
+        return fail(ctx, win_w <= 2 || win_h <= 2 ? SVO_GPU_E_ARG : SVO_GPU_E_UNSUPPORTED, "window %dx%d outside 3..%d",
+                    win_w, win_h, SVO_GPU_MAX_WIN);
+    if (max_level < 0) return fail(ctx, SVO_GPU_E_ARG, "maxLevel %d < 0", max_level);
+    if (max_level > ctx->max_levels - 1) max_level = ctx->max_levels - 1;
+    const int eff = effective_levels(s.w, s.h, win_w, win_h, max_level);
+    make_geometry(s.g, s.w, s.h, eff + 1, margin_for(win_w, win_h));
+    if (int r = ensure(ctx, s.pyr, (size_t)s.g.lane_bytes * (size_t)ctx->max_batch)) return r;
+    uint8_t* pyr = static_cast<uint8_t*>(s.pyr.p);
+    launch_ingest(ctx->st, s.raw, s.raw_pitch, s.raw_lane, pyr, s.g, s.batch, &ctx->launches);
+    for (int l = 1; l <= eff; ++l) launch_pyrdown(ctx->st, pyr, s.g, l, s.batch, &ctx->launches);
+    CK(cudaGetLastError());
+    s.pyr_built = true;
+    s.win_w = win_w; s.win_h = win_h;
+    if (levels_out) *levels_out = eff;
+    return 0;
+}
+
+extern "C" int svo_gpu_build_pyramid(svo_gpu_ctx* ctx, int slot, int win_w, int win_h, int max_level, int* levels_out)
+{
+    if (!ctx) return SVO_GPU_E_ARG;
+    if (int r = check_slot(ctx, slot)) return r;
+    DeviceGuard guard(ctx->device);
+    if (int r = enqueue_pyramid(ctx, ctx->slots[slot], win_w, win_h, max_level, levels_out)) return r;
+    CK(cudaStreamSynchronize(ctx->st));
+    return 0;
+}
+
+extern "C" int svo_gpu_download_level(svo_gpu_ctx* ctx, int slot, int lane, int level, uint8_t* host, int capacity_bytes,
+                                      int* w_out, int* h_out)
+{
+    if (!ctx) return SVO_GPU_E_ARG;
+    if (int r = check_slot(ctx, slot)) return r;
+    Slot& s = ctx->slots[slot];
+    if (!s.pyr_built) return fail(ctx, SVO_GPU_E_STATE, "pyramid of slot %d not built", slot);
+    if (level < 0 || level >= s.g.nlevels || lane < 0 || lane >= s.batch)
+        return fail(ctx, SVO_GPU_E_ARG, "level %d / lane %d out of range", level, lane);
+    const LevelGeom& L = s.g.lv[level];
+    if (w_out) *w_out = L.w;
+    if (h_out) *h_out = L.h;
+    if (!host || capacity_bytes < L.w * L.h) return fail(ctx, SVO_GPU_E_CAPACITY, "need %d bytes", L.w * L.h);
+    DeviceGuard guard(ctx->device);
+    const uint8_t* src = static_cast<const uint8_t*>(s.pyr.p) + (size_t)lane * s.g.lane_bytes + L.off;
+    CK(cudaMemcpy2DAsync(host, (size_t)L.w, src, (size_t)L.pitch, (size_t)L.w, (size_t)L.h, cudaMemcpyDeviceToHost, ctx->st));
+    CK(cudaStreamSynchronize(ctx->st));
+    return 0;
+}
+
+#include "capi_ops.inc"
+#include "capi_step.inc"

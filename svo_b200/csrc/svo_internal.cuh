@@ -1,0 +1,115 @@
+// svo_internal.cuh -- shared declarations of the sm_100a front-end kernels (not part of the public ABI).
+//
+// Layout of one image "slot" in HBM (per lane, i.e. per independent stream):
+//   raw      : the uploaded 8-bit image, row pitch raw_pitch (or an alias of caller-owned device memory)
+//   pyramid  : levels 0..L, each stored with a BORDER_REFLECT_101 margin of P pixels on every side so that the LK
+//              kernel reads (win+3)x(win+3) regions with unconditional aligned 32-bit loads.  Rows are 128 B-pitched;
+//              P is a multiple of 16, so interior row starts are 16 B aligned.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "svo_gpu.h"
+
+namespace svo {
+
+constexpr int kMaxLevels = SVO_GPU_MAX_LEVELS;
+
+struct LevelGeom {
+    int w, h;        // interior size
+    int pitch;       // bytes per padded row
+    int pad_;
+    long long off;   // byte offset of interior pixel (0,0) from the lane's pyramid base
+};
+
+struct PyrGeom {
+    int nlevels;     // number of valid levels (effective maxLevel + 1)
+    int P;           // margin in pixels
+    LevelGeom lv[kMaxLevels];
+    long long lane_bytes;   // stride between lanes
+};
+
+// REFLECT_101 index map (cv::BORDER_REFLECT_101), valid for any i when n >= 2 (loops for tiny n), n == 1 -> 0
+__host__ __device__ inline int reflect101(int i, int n)
+{
+    if (n == 1) return 0;
+    while (i < 0 || i >= n) i = i < 0 ? -i : 2 * n - 2 - i;
+    return i;
+}
+
+// ------------------------------------------------------------------------------------------------ pyramid.cu
+// raw image (pitch raw_pitch, lane stride raw_lane) -> padded level 0 of every lane
+void launch_ingest(cudaStream_t st, const uint8_t* raw, size_t raw_pitch, size_t raw_lane, uint8_t* pyr,
+                   const PyrGeom& g, int batch, long long* launches);
+// level l-1 -> level l (5x5 Gaussian pyrDown, margins included), every lane
+void launch_pyrdown(cudaStream_t st, uint8_t* pyr, const PyrGeom& g, int level, int batch, long long* launches);
+
+// ------------------------------------------------------------------------------------------------ fast.cu
+constexpr int kFastTW = 64;   // tile width: one (row, tile) segment holds at most 64 keypoints
+constexpr int kFastTH = 16;
+
+struct FastBufs {
+    // per lane strides are in elements of the respective type
+    int* rowtotal;        // [B][rows_cap]           keypoints per image row (atomic counters, zeroed per call)
+    uint8_t* segcnt;      // [B][rows_cap * ntx_cap] keypoints per (row, tile) segment
+    uint16_t* segkp;      // [B][rows_cap * ntx_cap * 64] x_local | best << 8, in x order inside a segment
+    int rows_cap, ntx_cap;
+    float2* kp_xy;        // [B][kp_cap]
+    float* kp_resp;       // [B][kp_cap]
+    int* kp_count;        // [B]  total keypoints found (may exceed kp_cap; only the first kp_cap are stored)
+    int kp_cap;
+};
+
+// mask: device u8 plane per lane (pitch mask_pitch, lane stride mask_lane) or nullptr
+void launch_fast(cudaStream_t st, const uint8_t* raw, size_t raw_pitch, size_t raw_lane, int w, int h, int threshold,
+                 int nms, const uint8_t* mask, size_t mask_pitch, size_t mask_lane, const FastBufs& fb, int batch,
+                 long long* launches);
+// mask plane = 255, then 0 in the rounded inclusive box around each point (src/tracking.cpp:76-79)
+// pts: [B][pts_lane] float2, n per lane from n_dev[lane] (device) clamped to n_max
+void launch_build_mask(cudaStream_t st, uint8_t* mask, size_t mask_pitch, size_t mask_lane, int w, int h,
+                       const float2* pts, size_t pts_lane, const int* n_dev, int n_max, float half, int batch,
+                       long long* launches);
+
+// ------------------------------------------------------------------------------------------------ bucket.cu
+struct BucketBufs {
+    int* cell_slots;      // [B][cells_cap * k_cap]  the k smallest input indices per bucket (INT_MAX = empty)
+    int* cell_cnt;        // [B][cells_cap]          arrivals per bucket
+    int* cell_last;       // [B][cells_cap]          largest input index per bucket
+    int* err_flag;        // [B]                     set when a point maps outside the bucket table
+    size_t cells_cap;     // per-lane capacity of cell_cnt / cell_last
+    size_t slots_cap;     // per-lane capacity of cell_slots
+    float2* out_xy;       // [B][out_cap]
+    int* out_age;         // [B][out_cap]
+    int* out_count;       // [B]  required output count (may exceed out_cap)
+    int out_cap;
+};
+
+// in_xy: [B][in_lane] float2; in_age may be nullptr (all ages 0, FeatureSet::appendNewFeatures, src/bucket.cpp:18-22);
+// n per lane = min(n_dev[lane], n_max)
+void launch_bucket(cudaStream_t st, const float2* in_xy, const int* in_age, size_t in_lane, const int* n_dev, int n_max,
+                   int img_w, int img_h, int bucket_size, int per_bucket, const BucketBufs& bb, int batch,
+                   long long* launches);
+
+// ------------------------------------------------------------------------------------------------ klt.cu
+struct KltArgs {
+    const uint8_t* prev_pyr;   // lane 0 base of the prev slot's pyramid
+    const uint8_t* next_pyr;
+    PyrGeom g;                 // same geometry for both slots
+    const float2* prev_xy;     // [B][pts_lane]
+    float2* next_xy;           // [B][pts_lane]
+    uint8_t* status;           // [B][pts_lane]
+    float* err;                // [B][pts_lane]
+    size_t pts_lane;
+    const int* n_dev;          // [B] points per lane (device), clamped to n_max
+    int n_max;
+    int win_w, win_h;
+    int max_level;             // effective
+    int max_count;             // already clamped like OpenCV
+    double eps2;               // epsilon^2, already clamped
+    int flags;
+    double min_eig_threshold;
+    unsigned long long* iters; // optional global iteration counter
+};
+void launch_klt(cudaStream_t st, const KltArgs& a, int batch, long long* launches);
+
+}  // namespace svo
