@@ -1,0 +1,355 @@
+#!/usr/bin/env python
+"""bench.py -- front-end frames/s of the svo per-frame feature front-end (FAST + bucketing + 4-level 21x21 KLT).
+
+One "step" = one frame of every stream on this GPU through svo_gpu_step (libsvo_gpu.so, C ABI): ingest + pyramid,
+LK from the previous frame on each stream's 2k tracks, FAST-9/16 + NMS on the new frame, grid bucketing, re-seeding of
+the tracks.  Workload = BASELINE.json's metric configuration (1241x376 KITTI-shaped synthetic frames, 2k tracks per
+stream) with `--streams` independent sequences per GPU (C5: 64).  Streams never interact, so N GPUs = N x streams
+sequences with no collective ("scaling": "weak"); torch.distributed is used for the start/stop barriers only.
+
+  value : frames/s with the frames already resident in HBM (device ring larger than L2), CUDA events on the context's stream
+  e2e   : frames/s through the same C-ABI call with HOST frames (pinned), H2D of every frame and D2H of the step's
+          results (tracked points, status, err, bucketed features, counts) inside the timed region
+  --impl reference : the reference's own CPU path (OpenCV via cv2 + src/bucket.cpp compiled unmodified) on the host cores
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+from concurrent.futures import ThreadPoolExecutor
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from svo_b200 import synth  # noqa: E402
+
+RING = 8   # frames per stream kept resident; time stamps 0,1,2,3,4,3,2,1 so that consecutive frames (and the wrap) are ~2 px apart
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=40)
+    ap.add_argument("--warmup", type=int, default=8)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--streams", type=int, default=64, help="independent sequences per GPU")
+    ap.add_argument("--workload", default="C1", choices=sorted(synth.WORKLOADS), help="per-stream shape")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
+    return ap.parse_args()
+
+
+def make_frames(wl, streams, seed0):
+    """uint8 [RING, streams, h, w]: stream s = synthetic sequence with seed seed0 + s."""
+    w, h = wl["w"], wl["h"]
+    times = synth.ring_times(RING)
+    distinct = sorted(set(times))
+
+    def one(s):
+        canvas = synth.make_canvas(w, h, seed0 + s)
+        fr = {t: synth.render_frame(canvas, w, h, t) for t in distinct}
+        return np.stack([fr[t] for t in times])
+
+    with ThreadPoolExecutor(max_workers=min(16, os.cpu_count() or 1)) as ex:
+        seqs = list(ex.map(one, range(streams)))
+    return np.ascontiguousarray(np.stack(seqs, axis=1))
+
+
+def step_params(wl):
+    return dict(fast_threshold=wl["fast_thr"], bucket_size=wl["bucket_size"], per_bucket=wl["per_bucket"],
+                max_tracks=wl["n_tracks"], win_w=wl["win"], win_h=wl["win"], max_level=wl["max_level"])
+
+
+def pyramid_pixels(w, h, levels):
+    n = 0
+    for _ in range(levels):
+        n += w * h
+        w, h = (w + 1) // 2, (h + 1) // 2
+    return n
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                       "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                      stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        for line in self.f.read().splitlines():
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1]))
+                mx.append(float(c[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), c[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        os.unlink(self.f.name)
+        if sm:
+            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+def dist_env():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+# ------------------------------------------------------------------------------------------------ CPU arm
+def cpu_frontend_run(frames, wl, n_streams, n_steps, warmup, threads):
+    """The reference's CPU path (cv2 + compiled src/bucket.cpp, else the C port) on `n_streams` streams for
+    `warmup + n_steps` frames each, streams spread over `threads` host threads.  Returns (seconds of the timed steps,
+    frames processed in them, kind)."""
+    from oracle import oracle as O                     # bench.py's CPU arm is one of the places allowed to run oracle/
+    from oracle.cpu_pipeline import CpuFrontend, default_params
+    O.build()
+    impl = "cv2" if O.have_cv2() else "orc"
+    if impl == "cv2":
+        import cv2
+        cv2.setNumThreads(1 if n_streams >= threads else threads)   # parallelism across streams when there are enough
+    p = default_params(wl["w"], wl["h"], wl["fast_thr"], wl["bucket_size"], wl["per_bucket"], wl["n_tracks"], wl["win"],
+                       wl["max_level"])
+    fes = [CpuFrontend(p, impl) for _ in range(n_streams)]
+    pool = ThreadPoolExecutor(max_workers=max(1, min(threads, n_streams)))
+
+    def run_step(t):
+        list(pool.map(lambda s: fes[s].step(frames[t % RING, s]), range(n_streams)))
+
+    for t in range(warmup):
+        run_step(t)
+    t0 = time.perf_counter()
+    for t in range(warmup, warmup + n_steps):
+        run_step(t)
+    dt = time.perf_counter() - t0
+    pool.shutdown()
+    return dt, n_streams * n_steps, ("reference" if impl == "cv2" else "port")
+
+
+def run_reference(args):
+    rank, _, world = dist_env()
+    if rank != 0:
+        return
+    wl = synth.WORKLOADS[args.workload]
+    threads = os.cpu_count() or 1
+    # bounded sample of the same workload: as many streams as host threads (each stream is sequential in time)
+    n_streams = min(args.streams * args.gpus, max(threads, 1))
+    frames = make_frames(wl, n_streams, wl["seed"] * 1000)
+    dt, nframes, kind = cpu_frontend_run(frames, wl, n_streams, args.steps, args.warmup, threads)
+    fps = nframes / dt
+    line = {
+        "impl": "reference", "metric": "front-end frames/s (FAST+bucketing+4-level 21x21 KLT, 2k tracks/stream)",
+        "value": fps, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8/int32 + f32 epilogue", "data": "synthetic",
+        "config": workload_config(args, wl, note="CPU arm: %d streams per step on %d host threads" % (n_streams, threads)),
+        "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": threads, "kind": kind,
+                         "sample": "%d streams x %d frames, cv2.setNumThreads(1), %d stream threads" %
+                                   (n_streams, args.steps, min(threads, n_streams))},
+        "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def workload_config(args, wl, note=None):
+    c = {"workload": "C5-shaped: %d independent %dx%d synthetic sequences per GPU, %d tracks each (C1 per stream: FAST thr %d "
+                     "+ NMS, bucketing %d px / %d per cell, KLT %dx%d, %d levels, 50 it / eps 0.001, min-eig err)" %
+                     (args.streams, wl["w"], wl["h"], wl["n_tracks"], wl["fast_thr"], wl["bucket_size"], wl["per_bucket"],
+                      wl["win"], wl["win"], wl["max_level"] + 1),
+         "streams_per_gpu": args.streams, "width": wl["w"], "height": wl["h"], "tracks_per_stream": wl["n_tracks"],
+         "parallelism": "independent sequences per GPU, no collective",
+         "l2": "frame ring of %d x %d frames (%.0f MB) cycled, larger than the 126 MB L2" %
+               (RING, args.streams, RING * args.streams * wl["h"] * 1280 / 1e6)}
+    if note:
+        c["note"] = note
+    return c
+
+
+# ------------------------------------------------------------------------------------------------ B200 arm
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from svo_b200 import capi
+    from svo_b200.frontend import Frontend
+
+    rank, local, world = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the front-end has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    wl = synth.WORKLOADS[args.workload]
+    w, h, S, K, W = wl["w"], wl["h"], args.streams, args.steps, args.warmup
+    levels = wl["max_level"] + 1
+    pitch = (w + 127) // 128 * 128
+
+    frames = make_frames(wl, S, wl["seed"] * 1000 + rank * S)            # [RING, S, h, w]
+    dev = torch.zeros((RING, S, h, pitch), dtype=torch.uint8, device="cuda")
+    dev[..., :w] = torch.from_numpy(frames).cuda()
+    host = torch.from_numpy(frames).pin_memory()                         # compact rows, like a cv::Mat
+    torch.cuda.synchronize()
+
+    cells = (h // wl["bucket_size"] + 1) * (w // wl["bucket_size"] + 1) * wl["per_bucket"]
+    ctx = capi.Context(device=local, max_w=w, max_h=h, max_levels=levels, max_points=max(32768, w * h // 16),
+                       max_batch=S)
+    fe = Frontend(ctx, w, h, S, bucket_capacity=cells, **step_params(wl))
+    stream = torch.cuda.ExternalStream(ctx.stream)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- end to end: host frames in, results out, every step (also yields the keypoint statistics)
+    fe.reset()
+    for i in range(W):
+        fe.step_host_ptr(host[i % RING].data_ptr(), w, w * h)
+    barrier()
+    ev[0].record(stream)
+    kp_sum = bk_sum = trk_sum = ok_sum = 0
+    for i in range(W, W + K):
+        fe.step_host_ptr(host[i % RING].data_ptr(), w, w * h)
+        kp_sum += int(fe.n_keypoints.sum()); bk_sum += int(fe.n_bucketed.sum()); trk_sum += int(fe.n_tracked.sum())
+        ok_sum += int(sum(int(fe.status[b, :fe.n_tracked[b]].sum()) for b in range(S)))
+    ev[1].record(stream)
+    barrier()
+    e2e_ms = max_over_ranks(ev[0].elapsed_time(ev[1]))
+
+    # ---- device resident: frames already in HBM, nothing returned to the host
+    fe.reset()
+    for i in range(W):
+        fe.step_device(dev[i % RING].data_ptr(), pitch, h * pitch)
+    ctx.step_profile(True)
+    launches0 = ctx.launch_count
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    ev[2].record(stream)
+    stage = np.zeros(4)
+    iters = 0
+    for i in range(W, W + K):
+        fe.step_device(dev[i % RING].data_ptr(), pitch, h * pitch)
+        stage += np.array(ctx.step_profile(True))
+        iters += ctx.last_klt_iterations
+    ev[3].record(stream)
+    barrier()
+    clocks = sampler.stop() if sampler else None
+    dev_ms = max_over_ranks(ev[2].elapsed_time(ev[3]))
+    launches = ctx.launch_count - launches0
+    ctx.step_profile(False)
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    frames_total = world * S * K
+    stage_ms = stage / K                                      # ingest+pyramid, LK, FAST, bucketing (per step, this rank)
+    kp = kp_sum / (S * K)
+    n_trk = trk_sum / (S * K)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
+    npyr = pyramid_pixels(w, h, levels)
+    # algorithmic bytes per launch group (SURVEY.md section 8d x the streams one launch covers)
+    alg = {
+        "pyramid": S * npyr,                                  # read level 0 once + write levels >= 1
+        "klt": S * (2 * npyr + 29 * n_trk),                   # both pyramids once + per-track in/out
+        "fast": S * (w * h + 12 * kp),
+        "bucket": S * 12 * (kp + bk_sum / (S * K)),
+    }
+    names = ["pyramid", "klt", "fast", "bucket"]
+    kernels = {n: {"ms": float(stage_ms[i]), "alg_bytes": float(alg[n]),
+                   "achieved_gbs": float(alg[n] / (stage_ms[i] * 1e-3) / 1e9) if stage_ms[i] > 0 else None}
+               for i, n in enumerate(names)}
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get("klt_kernel")
+    except Exception:
+        pass
+    klt = kernels["klt"]
+    it_per_track = iters / max(trk_sum, 1)
+    # op model of SURVEY 8d: 18 lane-ops per setup pixel per level, 8 per iteration pixel
+    lane_ops = (levels * wl["win"] ** 2 * 18 + it_per_track * wl["win"] ** 2 * 8) * n_trk * S
+    sm_mhz = (clocks or {}).get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)
+    line = {
+        "metric": "front-end frames/s (FAST+bucketing+4-level 21x21 KLT, 2k tracks/stream)",
+        "value": frames_total / (dev_ms * 1e-3), "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": W,
+        "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8/int32 + f32 epilogue", "data": "synthetic", "config": workload_config(args, wl),
+        "klt_tracks_per_s": world * trk_sum / K * K / (dev_ms * 1e-3) / K if K else None,
+        "e2e": {"value": frames_total / (e2e_ms * 1e-3), "unit": "frames/s", "h2d_bytes_per_step": S * w * h,
+                "d2h_bytes_per_step": fe.d2h_bytes, "ms_per_step": e2e_ms / K},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": {"kernel": "klt_kernel<21,21,8>", "bound": "hbm", "achieved": klt["achieved_gbs"], "peak": hbm_peak,
+                     "unit": "GB/s", "frac": (klt["achieved_gbs"] or 0) / hbm_peak, "traffic": traffic,
+                     "peak_source": peak_src,
+                     "note": "LK is not HBM-bound: its footprint (two pyramids) lives in L2; see klt_issue_model"},
+        "klt_issue_model": {"iterations_per_track": it_per_track, "lane_ops_per_launch": lane_ops,
+                            "achieved_lane_ops_per_s": lane_ops / (klt["ms"] * 1e-3) if klt["ms"] > 0 else None,
+                            "peak_lane_ops_per_s": 148 * 128 * sm_mhz * 1e6,
+                            "frac": (lane_ops / (klt["ms"] * 1e-3)) / (148 * 128 * sm_mhz * 1e6) if klt["ms"] > 0 else None},
+        "kernels": kernels,
+        "stats": {"keypoints_per_frame": kp, "bucketed_per_frame": bk_sum / (S * K), "tracks_per_frame": n_trk,
+                  "status_ok_frac": ok_sum / max(trk_sum, 1)},
+    }
+    line["klt_tracks_per_s"] = world * trk_sum / K * K / (dev_ms * 1e-3)
+    if world == 1 and not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        ns = min(S, threads)
+        nsteps = max(4, int(args.cpu_seconds / 0.06 / ns))
+        dt, nfr, kind = cpu_frontend_run(frames, wl, ns, nsteps, 2, threads)
+        line["cpu_baseline"] = {"value": nfr / dt, "unit": "frames/s", "cores": threads, "kind": kind,
+                                "sample": "%d streams x %d frames of the same workload, one stream per host thread" % (ns, nsteps)}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()
