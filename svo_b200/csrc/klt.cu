@@ -11,12 +11,17 @@
 //   - float32 epilogue in OpenCV's operation order with FMA contraction disabled (the file is compiled with -fmad=false)
 //   - status cleared only by level-0 outcomes; results are not clipped to the image.
 //
-// Design for sm_100a: the I patch, Ix, Iy of the feature live in REGISTERS (ceil(w*h/32) pixels per lane) for the
-// compiled window sizes (21x21, 11x11, 31x31); the (w+3)x(h+3) source region of each level is staged once per level in
-// the warp's slice of shared memory with aligned 32-bit loads from the REFLECT_101-margined pyramid (no bounds logic),
-// the Scharr derivative plane is computed there on the fly (the reference's int16x2 derivative images are never written
-// to HBM), and each Newton iteration stages the (w+1)x(h+1) region of the next image the same way.  Lanes never
-// diverge: all per-feature scalars are warp-uniform.  Other window sizes take the generic kernel (patch in shared memory).
+// Design for sm_100a (the kernel is instruction-issue bound, not HBM bound: its footprint, two pyramids, lives in L2):
+//   - the I patch, Ix, Iy of the feature live in REGISTERS (ceil(w*h/32) pixels per lane) for the compiled window
+//     sizes (21x21, 11x11, 31x31); other sizes take the generic instantiation (patch in shared memory)
+//   - source regions are staged per warp in shared memory with aligned 32-bit loads from the REFLECT_101-margined
+//     pyramid (no bounds logic), all loads of a region in flight before the first store
+//   - the reference's int16x2 Scharr derivative images are never materialised: because bilinear interpolation and the
+//     Scharr stencil are both integer-linear, sum_ij w_ij * Scharr(I)(p+ij) == Scharr(B)(p) with B = sum_ij w_ij * I(.+ij)
+//     the UNROUNDED bilinear plane, so the patch gradients come from one (w+2)x(h+2) int32 plane in shared memory.
+//     Windows that touch the image border (where OpenCV's derivative image is ZERO-padded, which breaks that identity)
+//     take the literal path: Scharr plane with zeros outside the image, then bilinear.
+//   - lanes never diverge: every per-feature scalar is warp-uniform.
 #include <float.h>
 
 #include "svo_internal.cuh"
@@ -51,46 +56,73 @@ __device__ __forceinline__ long long warp_sum_exact(int v)
     return ((long long)hi << 16) + (long long)lo;
 }
 
-// stage `nrows` rows of `nwords` aligned 32-bit words starting at the word that holds column x0 of row y0;
-// returns the byte offset (0..3) of column x0 inside the first word
+// unrounded bilinear sample at byte pointer p (row pitch rp)
+__device__ __forceinline__ int bilin(const uint8_t* __restrict__ p, int rp, const BiW& w)
+{
+    return (int)p[0] * w.w00 + (int)p[1] * w.w01 + (int)p[rp] * w.w10 + (int)p[rp + 1] * w.w11;
+}
+
+// Window geometry: compile-time for the specialised kernels (WW > 0), runtime otherwise.
+template <int WW, int WH>
+struct Geo {
+    static constexpr bool kFixed = WW > 0;
+    static constexpr int kNPL = kFixed ? (WW * WH + 31) / 32 : 1;   // patch pixels per lane (register-resident)
+    int ww_, wh_;
+    __device__ __forceinline__ Geo(int w, int h) : ww_(w), wh_(h) {}
+    __device__ __forceinline__ int ww() const { return kFixed ? WW : ww_; }
+    __device__ __forceinline__ int wh() const { return kFixed ? WH : wh_; }
+    __device__ __forceinline__ int npx() const { return ww() * wh(); }
+    __device__ __forceinline__ int nwords() const { return (ww() + 9) >> 2; }      // words per staged row
+    __device__ __forceinline__ int rpitch() const { return nwords() * 4; }          // bytes per staged row
+    __device__ __forceinline__ int bp() const { return ww() + 2; }                  // B plane row pitch (words)
+    __device__ __forceinline__ int region_words() const { return (wh() + 3) * nwords(); }
+    __device__ __forceinline__ int plane_words() const { return (ww() + 2) * (wh() + 2); }
+};
+
+// Stages `nrows` rows of nwords aligned 32-bit words, starting at the word holding column x0 of row y0, into sm
+// (row-major, nwords per row).  Lane (r0, c0) = (lane / nwords, lane % nwords) walks rows r0, r0 + rpi, ...; all loads
+// are issued before the first store.  Returns the byte offset (0..3) of column x0 inside the first word.
+template <int MAXIT>
 __device__ __forceinline__ int stage_region(uint32_t* __restrict__ sm, const uint8_t* __restrict__ origin, int pitch,
-                                            int x0, int y0, int nrows, int nwords, int lane)
+                                            int x0, int y0, int nrows, int nwords, int r0, int c0, int rpi)
 {
     const int a = x0 & 3;
-    const uint8_t* src = origin + (long long)y0 * pitch + (x0 - a);
-    const int total = nrows * nwords;
-    for (int i = lane; i < total; i += 32) {
-        const int r = i / nwords, c = i - r * nwords;
-        sm[i] = __ldg(reinterpret_cast<const uint32_t*>(src + (long long)r * pitch) + c);
+    const uint8_t* src = origin + (long long)(y0 + r0) * pitch + (x0 - a) + 4 * c0;
+    const long long step = (long long)rpi * pitch;
+    uint32_t* dst = sm + r0 * nwords + c0;
+    const int dstep = rpi * nwords;
+    if constexpr (MAXIT > 0) {
+        uint32_t v[MAXIT];
+#pragma unroll
+        for (int k = 0; k < MAXIT; ++k)
+            if (r0 + k * rpi < nrows) v[k] = __ldg(reinterpret_cast<const uint32_t*>(src + k * step));
+#pragma unroll
+        for (int k = 0; k < MAXIT; ++k)
+            if (r0 + k * rpi < nrows) dst[k * dstep] = v[k];
+    } else {
+        for (int r = r0; r < nrows; r += rpi, src += step, dst += dstep) *dst = __ldg(reinterpret_cast<const uint32_t*>(src));
     }
     return a;
 }
 
-template <int WW, int WH>
-struct Cfg {
-    static constexpr bool kFixed = WW > 0;
-    static constexpr int kNPL = kFixed ? (WW * WH + 31) / 32 : 1;   // patch pixels per lane (register-resident)
-};
-
-// WW, WH > 0: compiled window, patch in registers, static shared memory.  WW == 0: runtime window, patch in shared memory.
 template <int WW, int WH, int WARPS>
 __global__ void __launch_bounds__(WARPS * 32) klt_kernel(const KltArgs a)
 {
-    using C = Cfg<WW, WH>;
-    constexpr bool FIXED = C::kFixed;
-    constexpr int NPL = C::kNPL;
-    const int ww = FIXED ? WW : a.win_w;
-    const int wh = FIXED ? WH : a.win_h;
-    const int npx = ww * wh;
-    const int nwords = (ww + 9) >> 2;        // words per staged row
-    const int rpitch = nwords * 4;           // bytes per staged row
-    const int dpitch = ww + 1;               // derivative plane row pitch (words)
-    const int region_words = (wh + 3) * nwords;
-    const int deriv_words = (ww + 1) * (wh + 1);
+    using G = Geo<WW, WH>;
+    constexpr bool FIXED = G::kFixed;
+    constexpr int NPL = G::kNPL;
+    const G g(a.win_w, a.win_h);
+    const int ww = g.ww(), wh = g.wh(), npx = g.npx();
+    const int nwords = g.nwords(), rpitch = g.rpitch(), BP = g.bp();
+    const int region_words = g.region_words(), plane_words = g.plane_words();
+    // compile-time trip counts of the staging loops (0 = runtime loop)
+    constexpr int NW_CT = FIXED ? ((WW + 9) >> 2) : 1;
+    constexpr int RPI_CT = 32 / NW_CT;
+    constexpr int IT_I = FIXED ? (WH + 3 + RPI_CT - 1) / RPI_CT : 0;   // (wh+3)-row region of the previous image
+    constexpr int IT_J = FIXED ? (WH + 1 + RPI_CT - 1) / RPI_CT : 0;   // (wh+1)-row region of the next image
 
     extern __shared__ __align__(16) uint32_t smem_dyn[];
-    constexpr int kStaticWords =
-        FIXED ? WARPS * ((WH + 3) * ((WW + 9) >> 2) + (WW + 1) * (WH + 1)) : 1;
+    constexpr int kStaticWords = FIXED ? WARPS * ((WH + 3) * ((WW + 9) >> 2) + (WW + 2) * (WH + 2)) : 1;
     __shared__ __align__(16) uint32_t smem_static[kStaticWords];
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -99,25 +131,33 @@ __global__ void __launch_bounds__(WARPS * 32) klt_kernel(const KltArgs a)
     const int pt = blockIdx.x * WARPS + warp;
     if (pt >= n) return;
 
-    const int per_warp_words = region_words + deriv_words + (FIXED ? 0 : (3 * npx + 1) / 2);
+    const int per_warp_words = region_words + plane_words + (FIXED ? 0 : (3 * npx + 1) / 2);
     uint32_t* region = (FIXED ? smem_static : smem_dyn) + warp * per_warp_words;
-    uint32_t* deriv = region + region_words;
-    short* pIw = reinterpret_cast<short*>(deriv + deriv_words);   // generic only
+    int* plane = reinterpret_cast<int*>(region + region_words);   // B plane (fast path) or packed Scharr plane (border path)
+    short* pIw = reinterpret_cast<short*>(plane + plane_words);   // generic kernel only
     short* pIx = pIw + npx;
     short* pIy = pIx + npx;
     const uint8_t* rbytes = reinterpret_cast<const uint8_t*>(region);
 
-    // per-lane pixel assignment q = lane + 32 k  ->  (x, y) in the window
-    int offI[NPL], offD[NPL];
+    // staging map of this lane
+    const int rpi = 32 / nwords;
+    int st_r0 = lane / nwords;
+    const int st_c0 = lane - st_r0 * nwords;
+    if (st_r0 >= rpi) st_r0 = 1 << 20;   // spare lanes stage nothing
+    // plane map of this lane: element lane + 32 i sits at (u, v), advanced incrementally (no divisions in the loops)
+    const int pl_v0 = lane / BP, pl_u0 = lane - pl_v0 * BP;
+    const int pl_du = 32 % BP, pl_dv = 32 / BP;
+
+    // register-resident patch of the compiled windows: pixel q = lane + 32 k
+    int offI[NPL];
     int Iw[NPL], Ix[NPL], Iy[NPL];
     if constexpr (FIXED) {
 #pragma unroll
         for (int k = 0; k < NPL; ++k) {
             int q = lane + 32 * k;
-            if (q >= WW * WH) q = 0;   // padding pixel: reads pixel 0, contributes nothing (Ix = Iy = 0, see below)
-            const int y = q / WW, x = q - y * WW;
-            offI[k] = y * rpitch + x;
-            offD[k] = y * dpitch + x;
+            if (q >= WW * WH) q = 0;   // padding slot: reads pixel 0 and contributes nothing (Ix = Iy = 0)
+            const int y = q / WW;
+            offI[k] = y * rpitch + (q - y * WW);
         }
     }
 
@@ -152,54 +192,105 @@ __global__ void __launch_bounds__(WARPS * 32) klt_kernel(const KltArgs a)
 
         // ---- stage the (ww+3) x (wh+3) region of I whose top-left is (ipx-1, ipy-1)
         __syncwarp();
-        int ao = stage_region(region, Ppyr + L.off, L.pitch, ipx - 1, ipy - 1, wh + 3, nwords, lane);
+        int ao = stage_region<IT_I>(region, Ppyr + L.off, L.pitch, ipx - 1, ipy - 1, wh + 3, nwords, st_r0, st_c0, rpi);
         __syncwarp();
+        const uint8_t* rb = rbytes + ao;
 
-        // ---- Scharr derivative plane at (ipx..ipx+ww, ipy..ipy+wh): zero outside the image (calcScharrDeriv + BORDER_CONSTANT)
-        for (int d = lane; d < deriv_words; d += 32) {
-            const int dy = d / dpitch, dx = d - dy * dpitch;
-            const int X = ipx + dx, Y = ipy + dy;
-            uint32_t packed = 0;
-            if (X >= 0 && X < L.w && Y >= 0 && Y < L.h) {
-                const uint8_t* r0 = rbytes + dy * rpitch + ao + dx;   // row Y-1, column X-1
-                const uint8_t* r1 = r0 + rpitch;
-                const uint8_t* r2 = r1 + rpitch;
-                const int ix = 3 * ((int)r0[2] - (int)r0[0]) + 10 * ((int)r1[2] - (int)r1[0]) + 3 * ((int)r2[2] - (int)r2[0]);
-                const int iy = 3 * ((int)r2[0] - (int)r0[0]) + 10 * ((int)r2[1] - (int)r0[1]) + 3 * ((int)r2[2] - (int)r0[2]);
-                packed = ((uint32_t)ix & 0xffffu) | ((uint32_t)iy << 16);
-            }
-            deriv[d] = packed;
-        }
-        __syncwarp();
-
-        // ---- patch: Iw = I*32 (bilinear, DESCALE 9), Ixw, Iyw (bilinear, DESCALE 14); Gram sums in exact integers
+        // all derivative taps (ipx..ipx+ww, ipy..ipy+wh) inside the image?  (warp-uniform)
+        const bool interior = ipx >= 0 && ipy >= 0 && ipx + ww < L.w && ipy + wh < L.h;
         int sA11 = 0, sA12 = 0, sA22 = 0;
-        auto patch_px = [&](int oI, int oD, int& ival, int& ixval, int& iyval) {
-            const uint8_t* p = rbytes + oI + rpitch + 1 + ao;   // (ipx + x, ipy + y)
-            ival = descale((int)p[0] * w.w00 + (int)p[1] * w.w01 + (int)p[rpitch] * w.w10 + (int)p[rpitch + 1] * w.w11,
-                           kWBits - 5);
-            const uint32_t d00 = deriv[oD], d01 = deriv[oD + 1], d10 = deriv[oD + dpitch], d11 = deriv[oD + dpitch + 1];
-            ixval = descale((int)(short)(d00 & 0xffff) * w.w00 + (int)(short)(d01 & 0xffff) * w.w01 +
-                                (int)(short)(d10 & 0xffff) * w.w10 + (int)(short)(d11 & 0xffff) * w.w11, kWBits);
-            iyval = descale(((int)d00 >> 16) * w.w00 + ((int)d01 >> 16) * w.w01 + ((int)d10 >> 16) * w.w10 +
-                                ((int)d11 >> 16) * w.w11, kWBits);
-        };
-        if constexpr (FIXED) {
+        if (interior) {
+            // ---- B(u,v) = unrounded bilinear sample of I at (ipx-1+u, ipy-1+v), u in [0,ww+1], v in [0,wh+1]
+            {
+                int u = pl_u0, v = pl_v0;
+                for (int d = lane; d < plane_words; d += 32) {
+                    plane[d] = bilin(rb + v * rpitch + u, rpitch, w);
+                    u += pl_du; v += pl_dv;
+                    if (u >= BP) { u -= BP; ++v; }
+                }
+            }
+            __syncwarp();
+            // Iw = DESCALE(B, 9);  Ixw = DESCALE(Scharr_x(B), 14);  Iyw = DESCALE(Scharr_y(B), 14)   (integer linearity)
+            auto fast_px = [&](int q, int& iv, int& ixv, int& iyv) {
+                const int y = q / ww;
+                const int* c = plane + q + 2 * y + BP + 1;   // (x+1, y+1) in the plane
+                const int nw_ = c[-BP - 1], n_ = c[-BP], ne_ = c[-BP + 1], w_ = c[-1], e_ = c[1];
+                const int sw_ = c[BP - 1], s_ = c[BP], se_ = c[BP + 1];
+                iv = descale(c[0], kWBits - 5);
+                ixv = descale(3 * ((ne_ - nw_) + (se_ - sw_)) + 10 * (e_ - w_), kWBits);
+                iyv = descale(3 * ((sw_ - nw_) + (se_ - ne_)) + 10 * (s_ - n_), kWBits);
+            };
+            if constexpr (FIXED) {
 #pragma unroll
-            for (int k = 0; k < NPL; ++k) {
-                int iv, ixv, iyv;
-                patch_px(offI[k], offD[k], iv, ixv, iyv);
-                if (lane + 32 * k >= WW * WH) { ixv = 0; iyv = 0; }
-                Iw[k] = iv; Ix[k] = ixv; Iy[k] = iyv;
-                sA11 += ixv * ixv; sA12 += ixv * iyv; sA22 += iyv * iyv;
+                for (int k = 0; k < NPL; ++k) {
+                    const bool valid = lane + 32 * k < WW * WH;
+                    int iv, ixv, iyv;
+                    fast_px(valid ? lane + 32 * k : 0, iv, ixv, iyv);
+                    if (!valid) { ixv = 0; iyv = 0; }
+                    Iw[k] = iv; Ix[k] = ixv; Iy[k] = iyv;
+                    sA11 += ixv * ixv; sA12 += ixv * iyv; sA22 += iyv * iyv;
+                }
+            } else {
+                for (int q = lane; q < npx; q += 32) {
+                    int iv, ixv, iyv;
+                    fast_px(q, iv, ixv, iyv);
+                    pIw[q] = (short)iv; pIx[q] = (short)ixv; pIy[q] = (short)iyv;
+                    sA11 += ixv * ixv; sA12 += ixv * iyv; sA22 += iyv * iyv;
+                }
             }
         } else {
-            for (int q = lane; q < npx; q += 32) {
+            // ---- border path: Scharr plane at (ipx..ipx+ww, ipy..ipy+wh), ZERO outside the image (calcScharrDeriv +
+            //      BORDER_CONSTANT), then bilinear on I, Ix, Iy exactly as OpenCV does
+            const int dpitch = ww + 1;
+            const int deriv_words = dpitch * (wh + 1);
+            {
+                const int dv = 32 / dpitch, du = 32 - dv * dpitch;
+                int v = lane / dpitch, u = lane - v * dpitch;
+                for (int d = lane; d < deriv_words; d += 32) {
+                    const int X = ipx + u, Y = ipy + v;
+                    uint32_t packed = 0;
+                    if (X >= 0 && X < L.w && Y >= 0 && Y < L.h) {
+                        const uint8_t* r0 = rb + v * rpitch + u;   // row Y-1, column X-1
+                        const uint8_t* r1 = r0 + rpitch;
+                        const uint8_t* r2 = r1 + rpitch;
+                        const int ix = 3 * ((int)r0[2] - (int)r0[0]) + 10 * ((int)r1[2] - (int)r1[0]) + 3 * ((int)r2[2] - (int)r2[0]);
+                        const int iy = 3 * ((int)r2[0] - (int)r0[0]) + 10 * ((int)r2[1] - (int)r0[1]) + 3 * ((int)r2[2] - (int)r0[2]);
+                        packed = ((uint32_t)ix & 0xffffu) | ((uint32_t)iy << 16);
+                    }
+                    plane[d] = (int)packed;
+                    u += du; v += dv;
+                    if (u >= dpitch) { u -= dpitch; ++v; }
+                }
+            }
+            __syncwarp();
+            auto slow_px = [&](int q, int& iv, int& ixv, int& iyv) {
                 const int y = q / ww, x = q - y * ww;
-                int iv, ixv, iyv;
-                patch_px(y * rpitch + x, y * dpitch + x, iv, ixv, iyv);
-                pIw[q] = (short)iv; pIx[q] = (short)ixv; pIy[q] = (short)iyv;
-                sA11 += ixv * ixv; sA12 += ixv * iyv; sA22 += iyv * iyv;
+                iv = descale(bilin(rb + (y + 1) * rpitch + x + 1, rpitch, w), kWBits - 5);
+                const int* dp = plane + q + y;   // y * dpitch + x
+                const int d00 = dp[0], d01 = dp[1], d10 = dp[dpitch], d11 = dp[dpitch + 1];
+                ixv = descale((int)(short)(d00 & 0xffff) * w.w00 + (int)(short)(d01 & 0xffff) * w.w01 +
+                                  (int)(short)(d10 & 0xffff) * w.w10 + (int)(short)(d11 & 0xffff) * w.w11, kWBits);
+                iyv = descale((d00 >> 16) * w.w00 + (d01 >> 16) * w.w01 + (d10 >> 16) * w.w10 + (d11 >> 16) * w.w11, kWBits);
+            };
+            if constexpr (FIXED) {
+#pragma unroll 1
+                for (int k = 0; k < NPL; ++k) {   // rare path: keep it small (not unrolled); dynamic register indexing
+                    const bool valid = lane + 32 * k < WW * WH;   // is avoided by the switch-free select chain below
+                    int iv, ixv, iyv;
+                    slow_px(valid ? lane + 32 * k : 0, iv, ixv, iyv);
+                    if (!valid) { ixv = 0; iyv = 0; }
+#pragma unroll
+                    for (int j = 0; j < NPL; ++j)
+                        if (j == k) { Iw[j] = iv; Ix[j] = ixv; Iy[j] = iyv; }
+                    sA11 += ixv * ixv; sA12 += ixv * iyv; sA22 += iyv * iyv;
+                }
+            } else {
+                for (int q = lane; q < npx; q += 32) {
+                    int iv, ixv, iyv;
+                    slow_px(q, iv, ixv, iyv);
+                    pIw[q] = (short)iv; pIx[q] = (short)ixv; pIy[q] = (short)iyv;
+                    sA11 += ixv * ixv; sA12 += ixv * iyv; sA22 += iyv * iyv;
+                }
             }
         }
         const float A11 = __fmul_rn(__ll2float_rn(warp_sum_exact(sA11)), FLT_SCALE);
@@ -219,6 +310,27 @@ __global__ void __launch_bounds__(WARPS * 32) klt_kernel(const KltArgs a)
         }
         D = __fdiv_rn(1.f, D);
 
+        // one pass over the window at the staged position of the next image: exact integer sums of
+        // diff*Ix, diff*Iy (Newton step) or |diff| (L1 residual)
+        auto window_pass = [&](const uint8_t* jb, int& s1, int& s2, bool l1) {
+            s1 = 0; s2 = 0;
+            if constexpr (FIXED) {
+#pragma unroll
+                for (int k = 0; k < NPL; ++k) {
+                    const int diff = ((bilin(jb + offI[k], rpitch, w) + (1 << (kWBits - 6))) >> (kWBits - 5)) - Iw[k];
+                    if (l1) { if (lane + 32 * k < WW * WH) s1 += abs(diff); }
+                    else { s1 += diff * Ix[k]; s2 += diff * Iy[k]; }
+                }
+            } else {
+                for (int q = lane; q < npx; q += 32) {
+                    const int y = q / ww, x = q - y * ww;
+                    const int diff = descale(bilin(jb + y * rpitch + x, rpitch, w), kWBits - 5) - (int)pIw[q];
+                    if (l1) s1 += abs(diff);
+                    else { s1 += diff * (int)pIx[q]; s2 += diff * (int)pIy[q]; }
+                }
+            }
+        };
+
         nx = __fsub_rn(nx, halfx); ny = __fsub_rn(ny, halfy);
         float pdx = 0.f, pdy = 0.f;
         const uint8_t* Jorigin = Npyr + L.off;
@@ -231,28 +343,10 @@ __global__ void __launch_bounds__(WARPS * 32) klt_kernel(const KltArgs a)
             ++iters;
             w = bilinear_weights(__fsub_rn(nx, (float)inx), __fsub_rn(ny, (float)iny));
             __syncwarp();
-            ao = stage_region(region, Jorigin, L.pitch, inx, iny, wh + 1, nwords, lane);
+            ao = stage_region<IT_J>(region, Jorigin, L.pitch, inx, iny, wh + 1, nwords, st_r0, st_c0, rpi);
             __syncwarp();
-            int sb1 = 0, sb2 = 0;
-            if constexpr (FIXED) {
-#pragma unroll
-                for (int k = 0; k < NPL; ++k) {
-                    const uint8_t* p = rbytes + offI[k] + ao;
-                    const int v = (int)p[0] * w.w00 + (int)p[1] * w.w01 + (int)p[rpitch] * w.w10 + (int)p[rpitch + 1] * w.w11;
-                    const int diff = descale(v, kWBits - 5) - Iw[k];
-                    sb1 += diff * Ix[k];
-                    sb2 += diff * Iy[k];
-                }
-            } else {
-                for (int q = lane; q < npx; q += 32) {
-                    const int y = q / ww, x = q - y * ww;
-                    const uint8_t* p = rbytes + y * rpitch + x + ao;
-                    const int v = (int)p[0] * w.w00 + (int)p[1] * w.w01 + (int)p[rpitch] * w.w10 + (int)p[rpitch + 1] * w.w11;
-                    const int diff = descale(v, kWBits - 5) - (int)pIw[q];
-                    sb1 += diff * (int)pIx[q];
-                    sb2 += diff * (int)pIy[q];
-                }
-            }
+            int sb1, sb2;
+            window_pass(rbytes + ao, sb1, sb2, false);
             const float b1 = __fmul_rn(__ll2float_rn(warp_sum_exact(sb1)), FLT_SCALE);
             const float b2 = __fmul_rn(__ll2float_rn(warp_sum_exact(sb2)), FLT_SCALE);
             const float dx = __fmul_rn(__fsub_rn(__fmul_rn(A12, b2), __fmul_rn(A22, b1)), D);
@@ -278,25 +372,10 @@ __global__ void __launch_bounds__(WARPS * 32) klt_kernel(const KltArgs a)
             }
             w = bilinear_weights(__fsub_rn(qx, (float)iqx), __fsub_rn(qy, (float)iqy));
             __syncwarp();
-            ao = stage_region(region, Jorigin, L.pitch, iqx, iqy, wh + 1, nwords, lane);
+            ao = stage_region<IT_J>(region, Jorigin, L.pitch, iqx, iqy, wh + 1, nwords, st_r0, st_c0, rpi);
             __syncwarp();
-            int serr = 0;
-            if constexpr (FIXED) {
-#pragma unroll
-                for (int k = 0; k < NPL; ++k) {
-                    const uint8_t* p = rbytes + offI[k] + ao;
-                    const int v = (int)p[0] * w.w00 + (int)p[1] * w.w01 + (int)p[rpitch] * w.w10 + (int)p[rpitch + 1] * w.w11;
-                    const int diff = descale(v, kWBits - 5) - Iw[k];
-                    if (lane + 32 * k < WW * WH) serr += abs(diff);
-                }
-            } else {
-                for (int q = lane; q < npx; q += 32) {
-                    const int y = q / ww, x = q - y * ww;
-                    const uint8_t* p = rbytes + y * rpitch + x + ao;
-                    const int v = (int)p[0] * w.w00 + (int)p[1] * w.w01 + (int)p[rpitch] * w.w10 + (int)p[rpitch + 1] * w.w11;
-                    serr += abs(descale(v, kWBits - 5) - (int)pIw[q]);
-                }
-            }
+            int serr, unused;
+            window_pass(rbytes + ao, serr, unused, true);
             er = __fdiv_rn(__fmul_rn(__ll2float_rn(warp_sum_exact(serr)), 1.f), (float)(32 * ww * wh));
         }
     }
@@ -323,17 +402,13 @@ void launch_klt(cudaStream_t st, const KltArgs& a, int batch, long long* launche
     if (a.n_max <= 0) return;
     if (a.win_w == 21 && a.win_h == 21) launch_fixed<21, 21, 8>(st, a, batch);
     else if (a.win_w == 11 && a.win_h == 11) launch_fixed<11, 11, 8>(st, a, batch);
-    else if (a.win_w == 31 && a.win_h == 31) launch_fixed<31, 31, 8>(st, a, batch);
+    else if (a.win_w == 31 && a.win_h == 31) launch_fixed<31, 31, 4>(st, a, batch);
     else {
         constexpr int WARPS = 4;
         const int ww = a.win_w, wh = a.win_h;
-        const int words = (wh + 3) * ((ww + 9) >> 2) + (ww + 1) * (wh + 1) + (3 * ww * wh + 1) / 2;
+        const int words = (wh + 3) * ((ww + 9) >> 2) + (ww + 2) * (wh + 2) + (3 * ww * wh + 1) / 2;
         const size_t bytes = (size_t)WARPS * words * 4;
-        static bool attr_set = false;
-        if (!attr_set) {
-            cudaFuncSetAttribute(klt_kernel<0, 0, WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
-            attr_set = true;
-        }
+        cudaFuncSetAttribute(klt_kernel<0, 0, WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
         dim3 grid((a.n_max + WARPS - 1) / WARPS, batch);
         klt_kernel<0, 0, WARPS><<<grid, WARPS * 32, bytes, st>>>(a);
     }
