@@ -1,0 +1,66 @@
+#!/usr/bin/env python
+"""Summarise an ncu run brought back in gpurun_out/<tag>/ into profiles/ (text, committed).
+usage: scripts/ncu_summarize.py gpurun_out/<tag> profiles/<name>   -> <name>_launches.txt, <name>_kernels.txt
+"""
+import collections, csv, os, subprocess, sys
+
+src, dst = sys.argv[1], sys.argv[2]
+
+def launches():
+    p = os.path.join(src, "launches.csv")
+    if not os.path.exists(p):
+        return
+    rows = [r for r in csv.reader(open(p, errors="replace")) if len(r) > 5]
+    hdr, agg = None, collections.defaultdict(lambda: [0, 0.0])
+    for r in rows:
+        if r[0] == "ID":
+            hdr = r
+            continue
+        if hdr is None:
+            continue
+        d = dict(zip(hdr, r))
+        if d.get("Metric Name") != "gpu__time_duration.sum":
+            continue
+        v = float(d["Metric Value"].replace(",", ""))
+        u = d["Metric Unit"]
+        v = v / 1e3 if u in ("ns", "nsecond") else v * 1e3 if u in ("ms", "msecond") else v
+        k = d["Kernel Name"][:70]
+        agg[k][0] += 1
+        agg[k][1] += v
+    tot = sum(v[1] for v in agg.values())
+    with open(dst + "_launches.txt", "w") as f:
+        f.write("# ncu --metrics gpu__time_duration.sum --clock-control none (cold-cache, serialised: compare SHARES)\n")
+        f.write("# source: %s/launches.csv\n" % src)
+        for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+            f.write("%-72s n=%4d total_us=%10.1f avg_us=%8.1f share=%.3f\n" % (k, v[0], v[1], v[1] / v[0], v[1] / tot))
+
+WANT = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
+        "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+        "l1tex__throughput.avg.pct_of_peak_sustained_elapsed", "lts__throughput.avg.pct_of_peak_sustained_elapsed",
+        "sm__warps_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread", "launch__grid_size",
+        "launch__block_size", "launch__occupancy_limit_registers", "launch__occupancy_limit_shared_mem",
+        "smsp__inst_executed.sum", "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active",
+        "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum", "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum",
+        "smsp__issue_active.avg.pct_of_peak_sustained_active"]
+
+def kernels():
+    rep = os.path.join(src, "prof.ncu-rep")
+    if not os.path.exists(rep):
+        return
+    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(raw.splitlines()))
+    hdr, units = rows[0], rows[1]
+    idx = {h: i for i, h in enumerate(hdr)}
+    with open(dst + "_kernels.txt", "w") as f:
+        f.write("# ncu --set full --clock-control none; source: %s/prof.ncu-rep (one row block per captured launch)\n" % src)
+        for r in rows[2:]:
+            f.write("---- %s\n" % r[idx["Kernel Name"]][:110])
+            for w in WANT:
+                if w in idx:
+                    f.write("  %-72s %s %s\n" % (w, r[idx[w]], units[idx[w]]))
+
+launches()
+kernels()
