@@ -1,0 +1,115 @@
+// frontend_selftest.cpp -- drives the drop-in wrappers the way the reference's Tracking does and dumps the results, so
+// that tests/test_host_wrappers.py can compare them with the oracle.  Mirrors, in order:
+//   Tracking::extractFeatures        src/tracking.cpp:74-92   mask (cv::rectangle equivalent) -> detect -> KeyPoint::convert
+//   "todo feature bucketing"         src/tracking.cpp:88      FeatureSet::appendNewFeatures + bucketingFeatures
+//   Tracking::findLeftFeaturesInRight src/tracking.cpp:94-118 LK 11x11, 30 it, flags 0
+//   Tracking::trackFrames            src/tracking.cpp:154-179 LK 21x21, 50 it, OPTFLOW_LK_GET_MIN_EIGENVALS
+// usage: frontend_selftest <in.bin> <out.bin>     in.bin = int32 {w, h, n_prev, bucket_size, per_bucket}, image a, image b,
+//                                                  n_prev x float2 previously tracked points
+// Without a CUDA device every call must throw (no CPU fallback): `frontend_selftest --expect-no-gpu` checks exactly that.
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+#include "bucket.h"
+
+static void put(FILE* f, const void* p, size_t bytes) { fwrite(p, 1, bytes, f); }
+static void put_i(FILE* f, int v) { put(f, &v, sizeof v); }
+
+static void fill_box(cv::Mat& m, cv::Point2f a, cv::Point2f b)   // cv::rectangle(mask, a, b, 0, FILLED) for the compat Mat
+{
+    auto rnd = [](float v) { return (int)lrintf(v); };
+    int xa = rnd(a.x), ya = rnd(a.y), xb = rnd(b.x), yb = rnd(b.y);
+    xa = xa < 0 ? 0 : xa; ya = ya < 0 ? 0 : ya;
+    xb = xb >= m.cols ? m.cols - 1 : xb; yb = yb >= m.rows ? m.rows - 1 : yb;
+    for (int y = ya; y <= yb; ++y)
+        for (int x = xa; x <= xb; ++x) m.at<uchar>(y, x) = 0;
+}
+
+int main(int argc, char** argv)
+{
+    if (argc == 2 && !strcmp(argv[1], "--expect-no-gpu")) {
+        cv::Mat img(cv::Size(64, 64), CV_8UC1, 7);
+        std::vector<cv::KeyPoint> kps;
+        try {
+            svo::GpuFastDetector::create(20, true)->detect(img, kps);
+        } catch (const cv::Exception& e) {
+            printf("threw as expected: %s\n", e.what());
+            return 0;
+        }
+        fprintf(stderr, "detect() returned without a GPU: a CPU fallback must not exist\n");
+        return 1;
+    }
+    if (argc != 3) return 2;
+    FILE* fi = fopen(argv[1], "rb");
+    if (!fi) return 2;
+    int hdr[5];
+    if (fread(hdr, sizeof(int), 5, fi) != 5) return 2;
+    const int w = hdr[0], h = hdr[1], n_prev = hdr[2], bs = hdr[3], k = hdr[4];
+    cv::Mat a(h, w, CV_8UC1), b(h, w, CV_8UC1);
+    std::vector<cv::Point2f> prevPts((size_t)n_prev);
+    if (fread(a.data, 1, (size_t)w * h, fi) != (size_t)w * h || fread(b.data, 1, (size_t)w * h, fi) != (size_t)w * h) return 2;
+    if (n_prev && fread(prevPts.data(), sizeof(cv::Point2f), (size_t)n_prev, fi) != (size_t)n_prev) return 2;
+    fclose(fi);
+    FILE* fo = fopen(argv[2], "wb");
+    try {
+        // ---- extractFeatures: mask around the previous features, detect through the cv::Feature2D pointer
+        cv::Ptr<cv::FeatureDetector> mDetector = svo::GpuFastDetector::create(20, true);
+        cv::Mat mask(a.size(), CV_8UC1, 255);
+        for (const auto& p : prevPts) fill_box(mask, p - cv::Point2f(10, 10), p + cv::Point2f(10, 10));
+        std::vector<cv::KeyPoint> keypoints;
+        mDetector->detect(a, keypoints, mask);
+        std::vector<cv::Point2f> newPoints;
+        cv::KeyPoint::convert(keypoints, newPoints);
+        put_i(fo, (int)keypoints.size());
+        for (const auto& kp : keypoints) { put(fo, &kp.pt, 8); put(fo, &kp.response, 4); }
+        // the same keypoints with the mask built on the device
+        std::vector<cv::KeyPoint> kp2;
+        svo::detectFASTAvoiding(a, prevPts, 10.f, kp2, 20, true);
+        int same = kp2.size() == keypoints.size();
+        for (size_t i = 0; same && i < kp2.size(); ++i)
+            same = kp2[i].pt.x == keypoints[i].pt.x && kp2[i].pt.y == keypoints[i].pt.y && kp2[i].response == keypoints[i].response;
+        put_i(fo, same);
+        // ---- bucketing at the "todo" of :88
+        FeatureSet fs;
+        fs.appendNewFeatures(newPoints);
+        fs.bucketingFeatures(a, bs, k);
+        put_i(fo, fs.size());
+        put(fo, fs.points.data(), 8 * (size_t)fs.size());
+        put(fo, fs.ages.data(), 4 * (size_t)fs.size());
+        // ---- stereo-style LK (:101-105) and temporal LK (:160-165) on the bucketed points
+        for (int mode = 0; mode < 2; ++mode) {
+            std::vector<cv::Point2f> nextPts;
+            std::vector<uchar> status;
+            cv::Mat error;
+            if (mode == 0) {
+                cv::TermCriteria tc(cv::TermCriteria::COUNT + cv::TermCriteria::EPS, 30, 0.001);
+                svo::calcOpticalFlowPyrLK(a, b, fs.points, nextPts, status, error, cv::Size(11, 11), 3, tc);
+            } else {
+                cv::TermCriteria tc(cv::TermCriteria::COUNT + cv::TermCriteria::EPS, 50, 0.001);
+                svo::calcOpticalFlowPyrLK(a, b, fs.points, nextPts, status, error, cv::Size(21, 21), 3, tc,
+                                          cv::OPTFLOW_LK_GET_MIN_EIGENVALS);
+            }
+            put_i(fo, (int)nextPts.size());
+            put(fo, nextPts.data(), 8 * nextPts.size());
+            put(fo, status.data(), status.size());
+            put(fo, error.data, 4 * (size_t)error.rows);
+        }
+        // ---- empty inputs behave like OpenCV
+        std::vector<cv::Point2f> none, out;
+        std::vector<uchar> st;
+        cv::Mat er;
+        svo::calcOpticalFlowPyrLK(a, b, none, out, st, er);
+        std::vector<cv::KeyPoint> kp3(3);
+        mDetector->detect(cv::Mat(), kp3);
+        put_i(fo, (int)(out.size() + st.size() + kp3.size() + (er.empty() ? 0 : 1)));
+    } catch (const cv::Exception& e) {
+        fprintf(stderr, "frontend_selftest: %s\n", e.what());
+        fclose(fo);
+        return 1;
+    }
+    fclose(fo);
+    svo::releaseContexts();
+    return 0;
+}

@@ -1,0 +1,84 @@
+// svo_frontend.hpp -- host C++ face of the B200 feature front-end, with the signatures the reference's tracking.cpp
+// already calls, so the three call sites change by an identifier each:
+//
+//   src/tracking.cpp:54    mDetector = cv::FastFeatureDetector::create(thr, nms)   ->  svo::GpuFastDetector::create(thr, nms)
+//   src/tracking.cpp:82    mDetector->detect(frame->leftImg(), keypoints, mask)    ->  unchanged (virtual cv::Feature2D::detect)
+//   src/tracking.cpp:101   cv::calcOpticalFlowPyrLK(... Size(11,11), 3, tc)        ->  svo::calcOpticalFlowPyrLK(same arguments)
+//   src/tracking.cpp:160   cv::calcOpticalFlowPyrLK(... Size(21,21), 3, tc, flags) ->  svo::calcOpticalFlowPyrLK(same arguments)
+//   src/tracking.cpp:88    "// todo feature bucketing ???"                         ->  FeatureSet::bucketingFeatures (bucket.h)
+//
+// Everything numeric happens behind the C ABI of include/svo_gpu.h (libsvo_gpu.so, sm_100a kernels).  There is no CPU
+// fallback: a failing call throws cv::Exception carrying svo_gpu_last_error(), the way a failing OpenCV call would.
+#pragma once
+
+#if __has_include(<opencv2/core.hpp>) && !defined(SVO_FORCE_COMPAT_OPENCV)
+#include <opencv2/core.hpp>
+#include <opencv2/features2d.hpp>
+#include <opencv2/video/tracking.hpp>
+#else
+#include "compat/opencv2/core.hpp"
+#endif
+
+#include <vector>
+
+#include "svo_gpu.h"
+
+namespace svo {
+
+#ifdef SVO_COMPAT_OPENCV
+typedef const cv::Mat& ImageArg;       // the reference only ever passes cv::Mat here
+inline const cv::Mat& asMat(ImageArg a) { return a; }
+inline cv::Mat noImage() { return cv::Mat(); }
+#else
+typedef cv::InputArray ImageArg;
+inline cv::Mat asMat(ImageArg a) { return a.getMat(); }
+inline cv::InputArray noImage() { return cv::noArray(); }
+#endif
+
+// The calling thread's context on `device` (created on first use, grown when a larger image or more points arrive).
+// Tracking::trackFrames is a static member (include/tracking.h:34) with no object to hang state on, hence thread-local.
+svo_gpu_ctx* defaultContext(int device = 0, int min_w = 0, int min_h = 0, int min_points = 0);
+// Selects the CUDA device the wrappers below use on this thread (default 0): one host thread per GPU.
+void setDevice(int device);
+int currentDevice();
+// Releases this thread's contexts (otherwise released at thread exit).
+void releaseContexts();
+
+// cv::FastFeatureDetector stand-in: FAST-9/16, threshold, optional 3x3 NMS, optional mask; keypoints in raster order with
+// size 7, angle -1, response = score, octave 0, class_id -1, exactly as cv::FastFeatureDetector::detect returns them.
+class GpuFastDetector : public cv::Feature2D {
+public:
+    static cv::Ptr<GpuFastDetector> create(int threshold = 10, bool nonmaxSuppression = true);
+    GpuFastDetector(int threshold, bool nonmaxSuppression) : threshold_(threshold), nms_(nonmaxSuppression) {}
+#ifdef SVO_COMPAT_OPENCV
+    void detect(const cv::Mat& image, std::vector<cv::KeyPoint>& keypoints, const cv::Mat& mask = cv::Mat()) override;
+#else
+    void detect(cv::InputArray image, std::vector<cv::KeyPoint>& keypoints, cv::InputArray mask = cv::noArray()) override;
+#endif
+    void setThreshold(int t) { threshold_ = t; }
+    int getThreshold() const { return threshold_; }
+    void setNonmaxSuppression(bool f) { nms_ = f; }
+    bool getNonmaxSuppression() const { return nms_; }
+
+private:
+    int threshold_;
+    bool nms_;
+};
+
+// Free-function form of the same call.
+void detectFAST(const cv::Mat& image, std::vector<cv::KeyPoint>& keypoints, const cv::Mat& mask, int threshold, bool nms);
+
+// The reference's mask + detect pair in one device pass (src/tracking.cpp:76-82): the 255/0 mask around `tracked` points is
+// built on the GPU, so no w*h-byte mask crosses PCIe.  Same keypoints as building the mask with cv::rectangle.
+void detectFASTAvoiding(const cv::Mat& image, const std::vector<cv::Point2f>& tracked, float half,
+                        std::vector<cv::KeyPoint>& keypoints, int threshold, bool nms);
+
+// cv::calcOpticalFlowPyrLK with its full parameter list and defaults.  status: 0/1 per point; err: CV_32F n x 1.
+// OPTFLOW_USE_INITIAL_FLOW is not supported (the reference never sets it) and throws.
+void calcOpticalFlowPyrLK(const cv::Mat& prevImg, const cv::Mat& nextImg, const std::vector<cv::Point2f>& prevPts,
+                          std::vector<cv::Point2f>& nextPts, std::vector<uchar>& status, cv::Mat& err,
+                          cv::Size winSize = cv::Size(21, 21), int maxLevel = 3,
+                          cv::TermCriteria criteria = cv::TermCriteria(cv::TermCriteria::COUNT + cv::TermCriteria::EPS, 30, 0.01),
+                          int flags = 0, double minEigThreshold = 1e-4);
+
+}  // namespace svo

@@ -1,0 +1,91 @@
+"""The host C++ wrappers with the reference's call signatures (svo_b200/host: GpuFastDetector::detect,
+svo::calcOpticalFlowPyrLK, FeatureSet::bucketingFeatures), driven by svo_b200/lib/frontend_selftest the way
+Tracking::extractFeatures / findLeftFeaturesInRight / trackFrames drive OpenCV (src/tracking.cpp:74-118, :154-179).
+CPU: the wrappers build, and without a device they throw instead of falling back.  GPU: results equal the oracle's."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from svo_b200 import synth
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+EXE = os.path.join(ROOT, "svo_b200", "lib", "frontend_selftest")
+
+
+@pytest.fixture(scope="module")
+def exe():
+    if not os.path.exists(EXE):
+        import __graft_entry__ as g
+        g.build()
+    return EXE
+
+
+def test_wrappers_throw_without_gpu(exe):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    r = subprocess.run([exe, "--expect-no-gpu"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert "threw as expected" in r.stdout
+
+
+def test_reference_signatures_declared():
+    hdr = open(os.path.join(ROOT, "svo_b200", "host", "svo_frontend.hpp")).read()
+    bk = open(os.path.join(ROOT, "svo_b200", "host", "bucket.h")).read()
+    for needle in ("class GpuFastDetector : public cv::Feature2D", "void calcOpticalFlowPyrLK(", "cv::Size winSize = cv::Size(21, 21)",
+                   "int maxLevel = 3", "int flags = 0, double minEigThreshold = 1e-4"):
+        assert needle in hdr, needle
+    for needle in ("struct FeatureSet", "std::vector<cv::Point2f> points;", "std::vector<int> ages;",
+                   "void appendNewFeatures(const std::vector<cv::Point2f>& features)",
+                   "void bucketingFeatures(const cv::Mat& image, int bucket_size, int features_per_bucket);"):
+        assert needle in bk, needle
+
+
+@pytest.mark.gpu
+def test_wrappers_match_oracle(exe, oracle, tmp_path):
+    w, h, bs, k = 320, 240, 32, 5
+    canvas = synth.make_canvas(w, h, 5)
+    a, b = synth.render_frame(canvas, w, h, 0), synth.render_frame(canvas, w, h, 1)
+    prev = np.random.default_rng(1).uniform([0, 0], [w, h], (25, 2)).astype(np.float32)
+    fin, fout = tmp_path / "in.bin", tmp_path / "out.bin"
+    with open(fin, "wb") as f:
+        np.array([w, h, len(prev), bs, k], np.int32).tofile(f)
+        a.tofile(f)
+        b.tofile(f)
+        prev.tofile(f)
+    r = subprocess.run([exe, str(fin), str(fout)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    buf = open(fout, "rb").read()
+    off = 0
+
+    def take(dtype, n):
+        nonlocal off
+        out = np.frombuffer(buf, dtype, n, off)
+        off += out.nbytes
+        return out
+
+    K = int(take(np.int32, 1)[0])
+    kp = take(np.float32, 3 * K).reshape(K, 3)
+    mask = oracle.orc_build_mask(w, h, prev, 10.0)
+    oxy, oresp = oracle.orc_fast(a, 20, True, mask=mask)
+    assert K == len(oxy) and K > 100
+    assert np.array_equal(kp[:, :2], oxy) and np.array_equal(kp[:, 2], oresp)
+    assert int(take(np.int32, 1)[0]) == 1                    # device-built mask gave the same keypoints
+    nb = int(take(np.int32, 1)[0])
+    bxy = take(np.float32, 2 * nb).reshape(nb, 2)
+    bag = take(np.int32, nb)
+    ox, oa = oracle.orc_bucket(oxy, np.zeros(K, np.int32), w, h, bs, k)
+    assert np.array_equal(bxy, ox) and np.array_equal(bag, oa)
+    for mode in (dict(win=(11, 11), max_level=3, max_count=30, epsilon=0.001, flags=0),
+                 dict(win=(21, 21), max_level=3, max_count=50, epsilon=0.001, flags=8)):
+        n = int(take(np.int32, 1)[0])
+        assert n == nb
+        nxy = take(np.float32, 2 * n).reshape(n, 2)
+        st = take(np.uint8, n)
+        er = take(np.float32, n)
+        oxy2, ost, oer = oracle.orc_klt(a, b, bxy, **mode)
+        assert np.array_equal(st, ost) and np.array_equal(nxy, oxy2) and np.array_equal(er, oer)
+    assert int(take(np.int32, 1)[0]) == 0                    # empty inputs -> empty outputs, like OpenCV
+    assert off == len(buf)
