@@ -1,129 +1,163 @@
-// klt.cu -- K4: pyramidal Lucas-Kanade, one warp per feature, all pyramid levels in one launch.
+// klt.cu -- K4: pyramidal Lucas-Kanade for the compiled windows (21x21, 11x11, 31x31), one warp per feature, all
+// pyramid levels in one launch.  Other window sizes take klt_generic.cu.
 //
 // Replaces cv::calcOpticalFlowPyrLK at the reference's two call sites:
 //   temporal tracking  src/tracking.cpp:160-165  (21x21, maxLevel 3, {COUNT+EPS, 50, 0.001}, OPTFLOW_LK_GET_MIN_EIGENVALS)
 //   stereo matching    src/tracking.cpp:101-105  (11x11, maxLevel 3, {COUNT+EPS, 30, 0.001}, flags 0 -> L1 residual err)
-// The arithmetic is OpenCV's LKTrackerInvoker (video/src/lkpyramid.cpp, un-vendored), restated step by step in SURVEY.md
-// Appendix A.3-A.5 and in oracle/svo_oracle.c:orc_klt_ex (accum_mode 0), which this kernel matches bit for bit:
-//   - 14-bit integer bilinear weights, DESCALE roundings, int16-range patch values (I*32, Scharr Ix, Iy)
-//   - window sums (A11, A12, A22, b1, b2, L1 error) accumulated EXACTLY in integers (per-lane int32 partials, warp
-//     reduction with REDUX on 16-bit split halves), converted to float32 once
-//   - float32 epilogue in OpenCV's operation order with FMA contraction disabled (the file is compiled with -fmad=false)
-//   - status cleared only by level-0 outcomes; results are not clipped to the image.
+// The arithmetic is OpenCV's LKTrackerInvoker (video/src/lkpyramid.cpp, un-vendored), restated in SURVEY.md Appendix
+// A.3-A.5 and oracle/svo_oracle.c:orc_klt_ex (accum_mode 0), which this kernel matches bit for bit: 14-bit integer
+// bilinear weights, DESCALE roundings, window sums accumulated exactly in integers, float32 epilogue in OpenCV's
+// operation order (-fmad=false), status cleared only by level-0 outcomes, results not clipped to the image.
 //
-// Design for sm_100a (the kernel is instruction-issue bound, not HBM bound: its footprint, two pyramids, lives in L2):
-//   - the I patch, Ix, Iy of the feature live in REGISTERS (ceil(w*h/32) pixels per lane) for the compiled window
-//     sizes (21x21, 11x11, 31x31); other sizes take the generic instantiation (patch in shared memory)
-//   - source regions are staged per warp in shared memory with aligned 32-bit loads from the REFLECT_101-margined
-//     pyramid (no bounds logic), all loads of a region in flight before the first store
-//   - the reference's int16x2 Scharr derivative images are never materialised: because bilinear interpolation and the
-//     Scharr stencil are both integer-linear, sum_ij w_ij * Scharr(I)(p+ij) == Scharr(B)(p) with B = sum_ij w_ij * I(.+ij)
-//     the UNROUNDED bilinear plane, so the patch gradients come from one (w+2)x(h+2) int32 plane in shared memory.
-//     Windows that touch the image border (where OpenCV's derivative image is ZERO-padded, which breaks that identity)
-//     take the literal path: Scharr plane with zeros outside the image, then bilinear.
-//   - lanes never diverge: every per-feature scalar is warp-uniform.
-#include <float.h>
+// Design for sm_100a.  The kernel is issue-bound (its footprint, two pyramids, sits in L2), so the layout is chosen to
+// minimise instructions per window pixel:
+//   - a window row is cut into RUNS of 8 pixels; a lane owns RPL runs.  The 9 source bytes a run needs from each of its
+//     two image rows arrive as one 64-bit + one 32-bit shared-memory load, and the bilinear sample of a pixel is two
+//     DP2A instructions (u16 weight pair x u8 pixel pair, accumulated), instead of four byte loads and four multiply-adds.
+//   - source regions are staged per warp in shared memory ALREADY SHIFTED to the window's first column (aligned 32-bit
+//     global loads + funnel shift), rows 8*NSEG bytes apart, so run r of the window starts at byte 8 r: the lanes'
+//     64-bit loads are contiguous, hence bank-conflict free, and no per-pixel address arithmetic remains.
+//   - the patch (I*32, Ix, Iy) lives in registers for the whole level.
+//   - the reference's int16x2 Scharr derivative images are never materialised: bilinear interpolation and the Scharr
+//     stencil are both integer-linear, so sum_ij w_ij Scharr(I)(p+ij) == Scharr(B)(p) with B the UNROUNDED bilinear plane
+//     ((w+2)x(h+2) int32, built with the same run/DP2A scheme); a lane reads the 3x10 plane values of a run with 128-bit
+//     loads and forms Ix, Iy separably.  Windows that touch the image border (where OpenCV's derivative image is
+//     ZERO-padded, which breaks that identity) take the literal path: Scharr plane with zeros outside, then bilinear.
+//   - lanes never diverge: every per-feature scalar is warp-uniform; reductions are REDUX on 16-bit halves (exact).
+#include <type_traits>
 
-#include "svo_internal.cuh"
+#include "klt_common.cuh"
 
 namespace svo {
 
 namespace {
 
-constexpr unsigned kFull = 0xffffffffu;
-constexpr int kWBits = 14;
+using namespace lk;
 
-__device__ __forceinline__ int descale(int v, int n) { return (v + (1 << (n - 1))) >> n; }
-
-struct BiW { int w00, w01, w10, w11; };
-
-__device__ __forceinline__ BiW bilinear_weights(float a, float b)
-{
-    const float oa = __fsub_rn(1.f, a), ob = __fsub_rn(1.f, b);
-    BiW w;
-    w.w00 = __float2int_rn(__fmul_rn(__fmul_rn(oa, ob), 16384.f));
-    w.w01 = __float2int_rn(__fmul_rn(__fmul_rn(a, ob), 16384.f));
-    w.w10 = __float2int_rn(__fmul_rn(__fmul_rn(oa, b), 16384.f));
-    w.w11 = (1 << kWBits) - w.w00 - w.w01 - w.w10;
-    return w;
-}
-
-// exact warp sum of per-lane int32 partials (the total may need more than 32 bits): REDUX on the two 16-bit halves
-__device__ __forceinline__ long long warp_sum_exact(int v)
-{
-    const unsigned lo = __reduce_add_sync(kFull, (unsigned)(v & 0xffff));
-    const int hi = __reduce_add_sync(kFull, v >> 16);
-    return ((long long)hi << 16) + (long long)lo;
-}
-
-// unrounded bilinear sample at byte pointer p (row pitch rp)
-__device__ __forceinline__ int bilin(const uint8_t* __restrict__ p, int rp, const BiW& w)
-{
-    return (int)p[0] * w.w00 + (int)p[1] * w.w01 + (int)p[rp] * w.w10 + (int)p[rp + 1] * w.w11;
-}
-
-// Window geometry: compile-time for the specialised kernels (WW > 0), runtime otherwise.
 template <int WW, int WH>
-struct Geo {
-    static constexpr bool kFixed = WW > 0;
-    static constexpr int kNPL = kFixed ? (WW * WH + 31) / 32 : 1;   // patch pixels per lane (register-resident)
-    int ww_, wh_;
-    __device__ __forceinline__ Geo(int w, int h) : ww_(w), wh_(h) {}
-    __device__ __forceinline__ int ww() const { return kFixed ? WW : ww_; }
-    __device__ __forceinline__ int wh() const { return kFixed ? WH : wh_; }
-    __device__ __forceinline__ int npx() const { return ww() * wh(); }
-    __device__ __forceinline__ int nwords() const { return (ww() + 9) >> 2; }      // words per staged row
-    __device__ __forceinline__ int rpitch() const { return nwords() * 4; }          // bytes per staged row
-    __device__ __forceinline__ int bp() const { return ww() + 2; }                  // B plane row pitch (words)
-    __device__ __forceinline__ int region_words() const { return (wh() + 3) * nwords(); }
-    __device__ __forceinline__ int plane_words() const { return (ww() + 2) * (wh() + 2); }
+struct RunGeo {
+    static_assert(WW % 8 != 0 && (WW + 2) % 8 != 0, "window widths that are 0 or 6 mod 8 take the generic kernel");
+    static constexpr int NSEG = WW / 8 + 1;            // 8-pixel runs per window row (the last one partial)
+    static constexpr int RUNS = WH * NSEG;
+    static constexpr int RPL = (RUNS + 31) / 32;       // runs per lane
+    static constexpr int RPJ = 8 * NSEG;               // bytes per staged row of the next image (needs WW + 1)
+    static constexpr int JROWS = WH + 1;
+    static constexpr int NSEGB = (WW + 2) / 8 + 1;     // runs per row of the B plane (WW + 2 values per row)
+    static constexpr int RPI = 8 * NSEGB;              // bytes per staged row of the previous image (needs WW + 3)
+    static constexpr int IROWS = WH + 3;
+    static constexpr int BP = 8 * NSEGB;               // plane pitch in words
+    static constexpr int PROWS = WH + 2;
+    static constexpr int RUNSB = PROWS * NSEGB;
+    static constexpr int RPLB = (RUNSB + 31) / 32;
+    // staging works in whole passes of 32 / (RP/4) rows (no predicates): the region holds the rounded-up row counts
+    static constexpr int IROWS_ST = (IROWS + 32 / (RPI / 4) - 1) / (32 / (RPI / 4)) * (32 / (RPI / 4));
+    static constexpr int JROWS_ST = (JROWS + 32 / (RPJ / 4) - 1) / (32 / (RPJ / 4)) * (32 / (RPJ / 4));
+    static constexpr int REGION_WORDS = ((IROWS_ST * RPI > JROWS_ST * RPJ ? IROWS_ST * RPI : JROWS_ST * RPJ) / 4 + 4 + 3) & ~3;
+    static constexpr int PLANE_WORDS = (PROWS * BP + 8 + 3) & ~3;
+    static constexpr int WARP_WORDS = REGION_WORDS + PLANE_WORDS;
 };
 
-// Stages `nrows` rows of nwords aligned 32-bit words, starting at the word holding column x0 of row y0, into sm
-// (row-major, nwords per row).  Lane (r0, c0) = (lane / nwords, lane % nwords) walks rows r0, r0 + rpi, ...; all loads
-// are issued before the first store.  Returns the byte offset (0..3) of column x0 inside the first word.
-template <int MAXIT>
-__device__ __forceinline__ int stage_region(uint32_t* __restrict__ sm, const uint8_t* __restrict__ origin, int pitch,
-                                            int x0, int y0, int nrows, int nwords, int r0, int c0, int rpi)
+// The eight (byte i, byte i+1) pairs of a run, as DP2A operands: with w0 = bytes 0..3, w1 = 4..7, w2 = 8.. of the run,
+// pixel 0 = lo(w0), 1 = lo(s0), 2 = hi(w0), 3 = hi(s0), 4 = lo(w1), 5 = lo(s1), 6 = hi(w1), 7 = hi(s1),
+// where s0 = bytes 1..4 and s1 = bytes 5..8.
+struct RunRow {
+    uint32_t w0, w1, s0, s1;
+};
+
+// shared-memory accesses by 32-bit shared-window address (keeps the address arithmetic out of the inner loops)
+__device__ __forceinline__ void sts32(uint32_t addr, uint32_t v)
 {
-    const int a = x0 & 3;
-    const uint8_t* src = origin + (long long)(y0 + r0) * pitch + (x0 - a) + 4 * c0;
-    const long long step = (long long)rpi * pitch;
-    uint32_t* dst = sm + r0 * nwords + c0;
-    const int dstep = rpi * nwords;
-    if constexpr (MAXIT > 0) {
-        uint32_t v[MAXIT];
-#pragma unroll
-        for (int k = 0; k < MAXIT; ++k)
-            if (r0 + k * rpi < nrows) v[k] = __ldg(reinterpret_cast<const uint32_t*>(src + k * step));
-#pragma unroll
-        for (int k = 0; k < MAXIT; ++k)
-            if (r0 + k * rpi < nrows) dst[k * dstep] = v[k];
-    } else {
-        for (int r = r0; r < nrows; r += rpi, src += step, dst += dstep) *dst = __ldg(reinterpret_cast<const uint32_t*>(src));
-    }
-    return a;
+    asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ void sts128(uint32_t addr, int4 v)
+{
+    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ uint32_t lds32(uint32_t addr)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint2 lds64(uint32_t addr)
+{
+    uint2 v;
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ int4 lds128(uint32_t addr)
+{
+    int4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+    return v;
 }
 
-template <int WW, int WH, int WARPS>
-__global__ void __launch_bounds__(WARPS * 32) klt_kernel(const KltArgs a)
+__device__ __forceinline__ RunRow load_run_row(uint32_t addr)
 {
-    using G = Geo<WW, WH>;
-    constexpr bool FIXED = G::kFixed;
-    constexpr int NPL = G::kNPL;
-    const G g(a.win_w, a.win_h);
-    const int ww = g.ww(), wh = g.wh(), npx = g.npx();
-    const int nwords = g.nwords(), rpitch = g.rpitch(), BP = g.bp();
-    const int region_words = g.region_words(), plane_words = g.plane_words();
-    // compile-time trip counts of the staging loops (0 = runtime loop)
-    constexpr int NW_CT = FIXED ? ((WW + 9) >> 2) : 1;
-    constexpr int RPI_CT = 32 / NW_CT;
-    constexpr int IT_I = FIXED ? (WH + 3 + RPI_CT - 1) / RPI_CT : 0;   // (wh+3)-row region of the previous image
-    constexpr int IT_J = FIXED ? (WH + 1 + RPI_CT - 1) / RPI_CT : 0;   // (wh+1)-row region of the next image
+    const uint2 a = lds64(addr);
+    const uint32_t b = lds32(addr + 8);
+    RunRow r;
+    r.w0 = a.x;
+    r.w1 = a.y;
+    r.s0 = __funnelshift_r(a.x, a.y, 8);
+    r.s1 = __funnelshift_r(a.y, b, 8);
+    return r;
+}
 
-    extern __shared__ __align__(16) uint32_t smem_dyn[];
-    constexpr int kStaticWords = FIXED ? WARPS * ((WH + 3) * ((WW + 9) >> 2) + (WW + 2) * (WH + 2)) : 1;
-    __shared__ __align__(16) uint32_t smem_static[kStaticWords];
+// d = c + a.lo16 * b.byte[0 or 2] + a.hi16 * b.byte[1 or 3]: SIGNED 16-bit weights (iw11 = 2^14 - iw00 - iw01 - iw10 can
+// come out as -1 when the three roundings all go up), UNSIGNED 8-bit pixels.
+__device__ __forceinline__ int dp2a_lo_su(uint32_t a, uint32_t b, int c)
+{
+    int d;
+    asm("dp2a.lo.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ int dp2a_hi_su(uint32_t a, uint32_t b, int c)
+{
+    int d;
+    asm("dp2a.hi.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ uint32_t pack_weights(int lo, int hi) { return ((uint32_t)lo & 0xffffu) | ((uint32_t)hi << 16); }
+
+template <int I>
+__device__ __forceinline__ int run_px(const RunRow& top, const RunRow& bot, uint32_t wt, uint32_t wb, int c)
+{
+    const uint32_t t = (I & 4) ? ((I & 1) ? top.s1 : top.w1) : ((I & 1) ? top.s0 : top.w0);
+    const uint32_t b = (I & 4) ? ((I & 1) ? bot.s1 : bot.w1) : ((I & 1) ? bot.s0 : bot.w0);
+    if (I & 2) return dp2a_hi_su(wb, b, dp2a_hi_su(wt, t, c));
+    return dp2a_lo_su(wb, b, dp2a_lo_su(wt, t, c));
+}
+
+// Stages rows of RP bytes whose first byte is column x0 of row y0 (any alignment) into shared memory, rows RP bytes
+// apart: two aligned 32-bit loads + one funnel shift per output word, all loads issued before the first store.
+// Works in PASSES whole passes of 32 / (RP/4) rows, so ROWS is rounded up (the pyramid margin covers the extra rows) and
+// no lane needs a predicate; lanes beyond the last full row of a pass repeat the work of the last row (same values).
+// src0 = address of the word holding (x0, y0 + r0) + 4 c0 for this lane's (r0, c0); dst0 = shared address of (r0, c0).
+template <int ROWS, int RP>
+__device__ __forceinline__ void stage_shifted(uint32_t dst0, const uint8_t* __restrict__ src0, int pitch, int x0)
+{
+    constexpr int OW = RP / 4, RPP = 32 / OW, PASSES = (ROWS + RPP - 1) / RPP;
+    const int sh = 8 * (x0 & 3);
+    uint32_t lo[PASSES], hi[PASSES];
+#pragma unroll
+    for (int k = 0; k < PASSES; ++k) {
+        const uint8_t* p = src0 + (long long)(k * RPP) * pitch;
+        lo[k] = __ldg(reinterpret_cast<const uint32_t*>(p));
+        hi[k] = __ldg(reinterpret_cast<const uint32_t*>(p + 4));
+    }
+#pragma unroll
+    for (int k = 0; k < PASSES; ++k) sts32(dst0 + k * RPP * RP, __funnelshift_r(lo[k], hi[k], sh));
+}
+
+template <int WW, int WH, int WARPS, bool PACKG>
+__global__ void __launch_bounds__(WARPS * 32) klt_run_kernel(const KltArgs a)
+{
+    using G = RunGeo<WW, WH>;
+    constexpr int RPL = G::RPL, BP = G::BP;
+    constexpr int NG = PACKG ? 1 : 2;   // registers per pixel for the gradients
+
+    __shared__ __align__(16) uint32_t smem[WARPS * G::WARP_WORDS];
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int lane_id = blockIdx.y;
@@ -131,47 +165,50 @@ __global__ void __launch_bounds__(WARPS * 32) klt_kernel(const KltArgs a)
     const int pt = blockIdx.x * WARPS + warp;
     if (pt >= n) return;
 
-    const int per_warp_words = region_words + plane_words + (FIXED ? 0 : (3 * npx + 1) / 2);
-    uint32_t* region = (FIXED ? smem_static : smem_dyn) + warp * per_warp_words;
-    int* plane = reinterpret_cast<int*>(region + region_words);   // B plane (fast path) or packed Scharr plane (border path)
-    short* pIw = reinterpret_cast<short*>(plane + plane_words);   // generic kernel only
-    short* pIx = pIw + npx;
-    short* pIy = pIx + npx;
+    uint32_t* region = smem + warp * G::WARP_WORDS;
+    int* plane = reinterpret_cast<int*>(region + G::REGION_WORDS);
     const uint8_t* rbytes = reinterpret_cast<const uint8_t*>(region);
 
-    // staging map of this lane
-    const int rpi = 32 / nwords;
-    int st_r0 = lane / nwords;
-    const int st_c0 = lane - st_r0 * nwords;
-    if (st_r0 >= rpi) st_r0 = 1 << 20;   // spare lanes stage nothing
-    // plane map of this lane: element lane + 32 i sits at (u, v), advanced incrementally (no divisions in the loops)
-    const int pl_v0 = lane / BP, pl_u0 = lane - pl_v0 * BP;
-    const int pl_du = 32 % BP, pl_dv = 32 / BP;
-
-    // register-resident patch of the compiled windows: pixel q = lane + 32 k
-    int offI[NPL];
-    int Iw[NPL], Ix[NPL], Iy[NPL];
-    if constexpr (FIXED) {
+    // ---- per-lane constants: staging maps, and for each owned run its offsets and number of valid pixels
+    constexpr int OWI = G::RPI / 4, OWJ = G::RPJ / 4;
+    const uint32_t region_sa = (uint32_t)__cvta_generic_to_shared(region);   // 32-bit shared-window addresses
+    const uint32_t plane_sa = (uint32_t)__cvta_generic_to_shared(plane);
+    const int sI_r = min(lane / OWI, 32 / OWI - 1), sI_c = lane % OWI;       // staging maps: lane -> (row, word) of a pass;
+    const int sJ_r = min(lane / OWJ, 32 / OWJ - 1), sJ_c = lane % OWJ;       // spare lanes repeat a word of the last row
+    const uint32_t sI_dst = region_sa + 4 * (sI_r * OWI + sI_c), sJ_dst = region_sa + 4 * (sJ_r * OWJ + sJ_c);
+    uint32_t jo[RPL], po[RPL];
+    int nval[RPL];
 #pragma unroll
-        for (int k = 0; k < NPL; ++k) {
-            int q = lane + 32 * k;
-            if (q >= WW * WH) q = 0;   // padding slot: reads pixel 0 and contributes nothing (Ix = Iy = 0)
-            const int y = q / WW;
-            offI[k] = y * rpitch + (q - y * WW);
-        }
+    for (int j = 0; j < RPL; ++j) {
+        const int r = lane + 32 * j;
+        const int rr = min(r, G::RUNS - 1);
+        const int y = rr / G::NSEG, seg = rr - y * G::NSEG;
+        jo[j] = region_sa + 8 * rr;     // shared address of the run in the staged next-image region (rows RPJ = 8 NSEG apart)
+        po[j] = plane_sa + 4 * (y * BP + 8 * seg);   // shared address of plane element (x, y), x = the run's first pixel
+        nval[j] = r < G::RUNS ? min(8, WW - 8 * seg) : 0;
     }
+
+    int Iw[RPL][8], Gx[RPL][8 * NG];   // Gx: Ix then Iy (NG == 2) or (Ix & 0xffff) | (Iy << 16) (PACKG)
 
     const size_t pbase = (size_t)lane_id * a.pts_lane + pt;
     const float2 prev = a.prev_xy[pbase];
     const uint8_t* Ppyr = a.prev_pyr + (size_t)lane_id * a.g.lane_bytes;
     const uint8_t* Npyr = a.next_pyr + (size_t)lane_id * a.g.lane_bytes;
 
-    const float halfx = (ww - 1) * 0.5f, halfy = (wh - 1) * 0.5f;
+    const float halfx = (WW - 1) * 0.5f, halfy = (WH - 1) * 0.5f;
     const float FLT_SCALE = 1.f / (1 << 20);
     float ox = 0.f, oy = 0.f;   // nextPts[pt]
     int st = 1;
     float er = 0.f;
     unsigned iters = 0;
+
+    auto set_px = [&](int j, int i, int iv, int ixv, int iyv) {
+        Iw[j][i] = iv;
+        if constexpr (PACKG) Gx[j][i] = (ixv & 0xffff) | (iyv << 16);
+        else { Gx[j][i] = ixv; Gx[j][8 + i] = iyv; }
+    };
+    auto get_ix = [&](int j, int i) { if constexpr (PACKG) return (int)(short)(Gx[j][i] & 0xffff); else return Gx[j][i]; };
+    auto get_iy = [&](int j, int i) { if constexpr (PACKG) return Gx[j][i] >> 16; else return Gx[j][8 + i]; };
 
     for (int level = a.max_level; level >= 0; --level) {
         const LevelGeom L = a.g.lv[level];
@@ -184,111 +221,115 @@ __global__ void __launch_bounds__(WARPS * 32) klt_kernel(const KltArgs a)
 
         px = __fsub_rn(px, halfx); py = __fsub_rn(py, halfy);
         const int ipx = (int)floorf(px), ipy = (int)floorf(py);
-        if (ipx < -ww || ipx >= L.w || ipy < -wh || ipy >= L.h) {
+        if (ipx < -WW || ipx >= L.w || ipy < -WH || ipy >= L.h) {
             if (level == 0) { st = 0; er = 0.f; }
             continue;
         }
         BiW w = bilinear_weights(__fsub_rn(px, (float)ipx), __fsub_rn(py, (float)ipy));
 
-        // ---- stage the (ww+3) x (wh+3) region of I whose top-left is (ipx-1, ipy-1)
+        // ---- stage the (WW+3) x (WH+3) region of I whose top-left is (ipx-1, ipy-1); staged byte (u, v) = I(ipx-1+u, ipy-1+v)
         __syncwarp();
-        int ao = stage_region<IT_I>(region, Ppyr + L.off, L.pitch, ipx - 1, ipy - 1, wh + 3, nwords, st_r0, st_c0, rpi);
+        {
+            const int x0 = ipx - 1;
+            const uint8_t* src0 = Ppyr + L.off + (long long)(ipy - 1 + sI_r) * L.pitch + ((x0 & ~3) + 4 * sI_c);
+            stage_shifted<G::IROWS, G::RPI>(sI_dst, src0, L.pitch, x0);
+        }
         __syncwarp();
-        const uint8_t* rb = rbytes + ao;
 
-        // all derivative taps (ipx..ipx+ww, ipy..ipy+wh) inside the image?  (warp-uniform)
-        const bool interior = ipx >= 0 && ipy >= 0 && ipx + ww < L.w && ipy + wh < L.h;
+        // all derivative taps (ipx..ipx+WW, ipy..ipy+WH) inside the image?  (warp-uniform)
+        const bool interior = ipx >= 0 && ipy >= 0 && ipx + WW < L.w && ipy + WH < L.h;
         int sA11 = 0, sA12 = 0, sA22 = 0;
         if (interior) {
-            // ---- B(u,v) = unrounded bilinear sample of I at (ipx-1+u, ipy-1+v), u in [0,ww+1], v in [0,wh+1]
+            // ---- B(u,v) = unrounded bilinear sample of I at (ipx-1+u, ipy-1+v): plane run rb covers u = 8 seg .. 8 seg + 7
+            //      of row v, and sits at word 8 rb of the plane / byte 8 rb of the region (both pitches are 8 NSEGB)
             {
-                int u = pl_u0, v = pl_v0;
-                for (int d = lane; d < plane_words; d += 32) {
-                    plane[d] = bilin(rb + v * rpitch + u, rpitch, w);
-                    u += pl_du; v += pl_dv;
-                    if (u >= BP) { u -= BP; ++v; }
+                const uint32_t wt = pack_weights(w.w00, w.w01), wb = pack_weights(w.w10, w.w11);
+#pragma unroll
+                for (int j = 0; j < G::RPLB; ++j) {
+                    const int rb = lane + 32 * j;
+                    if (rb < G::RUNSB) {
+                        const RunRow top = load_run_row(region_sa + 8 * rb), bot = load_run_row(region_sa + 8 * rb + G::RPI);
+                        int4 lo4, hi4;
+                        lo4.x = run_px<0>(top, bot, wt, wb, 0); lo4.y = run_px<1>(top, bot, wt, wb, 0);
+                        lo4.z = run_px<2>(top, bot, wt, wb, 0); lo4.w = run_px<3>(top, bot, wt, wb, 0);
+                        hi4.x = run_px<4>(top, bot, wt, wb, 0); hi4.y = run_px<5>(top, bot, wt, wb, 0);
+                        hi4.z = run_px<6>(top, bot, wt, wb, 0); hi4.w = run_px<7>(top, bot, wt, wb, 0);
+                        sts128(plane_sa + 32 * rb, lo4);
+                        sts128(plane_sa + 32 * rb + 16, hi4);
+                    }
                 }
             }
             __syncwarp();
-            // Iw = DESCALE(B, 9);  Ixw = DESCALE(Scharr_x(B), 14);  Iyw = DESCALE(Scharr_y(B), 14)   (integer linearity)
-            auto fast_px = [&](int q, int& iv, int& ixv, int& iyv) {
-                const int y = q / ww;
-                const int* c = plane + q + 2 * y + BP + 1;   // (x+1, y+1) in the plane
-                const int nw_ = c[-BP - 1], n_ = c[-BP], ne_ = c[-BP + 1], w_ = c[-1], e_ = c[1];
-                const int sw_ = c[BP - 1], s_ = c[BP], se_ = c[BP + 1];
-                iv = descale(c[0], kWBits - 5);
-                ixv = descale(3 * ((ne_ - nw_) + (se_ - sw_)) + 10 * (e_ - w_), kWBits);
-                iyv = descale(3 * ((sw_ - nw_) + (se_ - ne_)) + 10 * (s_ - n_), kWBits);
-            };
-            if constexpr (FIXED) {
+            // ---- Iw = DESCALE(B, 9);  Ixw = DESCALE(Scharr_x(B), 14);  Iyw = DESCALE(Scharr_y(B), 14)   (integer linearity)
+            //      separably: cs(u) = 3 B(u,v-1) + 10 B(u,v) + 3 B(u,v+1), rd(u) = B(u,v+1) - B(u,v-1);
+            //      Scharr_x = cs(u+1) - cs(u-1), Scharr_y = 3 rd(u-1) + 10 rd(u) + 3 rd(u+1)
 #pragma unroll
-                for (int k = 0; k < NPL; ++k) {
-                    const bool valid = lane + 32 * k < WW * WH;
-                    int iv, ixv, iyv;
-                    fast_px(valid ? lane + 32 * k : 0, iv, ixv, iyv);
-                    if (!valid) { ixv = 0; iyv = 0; }
-                    Iw[k] = iv; Ix[k] = ixv; Iy[k] = iyv;
-                    sA11 += ixv * ixv; sA12 += ixv * iyv; sA22 += iyv * iyv;
+            for (int j = 0; j < RPL; ++j) {
+                int cs[10], rd[10], mid[10];
+                {
+                    int r0[10], r2[10];
+                    auto load10 = [](uint32_t sa, int* d) {
+                        const int4 x = lds128(sa), y = lds128(sa + 16);
+                        const uint2 z = lds64(sa + 32);
+                        d[0] = x.x; d[1] = x.y; d[2] = x.z; d[3] = x.w; d[4] = y.x; d[5] = y.y; d[6] = y.z; d[7] = y.w;
+                        d[8] = (int)z.x; d[9] = (int)z.y;
+                    };
+                    load10(po[j], r0);
+                    load10(po[j] + 4 * BP, mid);
+                    load10(po[j] + 8 * BP, r2);
+#pragma unroll
+                    for (int u = 0; u < 10; ++u) {
+                        cs[u] = 3 * (r0[u] + r2[u]) + 10 * mid[u];
+                        rd[u] = r2[u] - r0[u];
+                    }
                 }
-            } else {
-                for (int q = lane; q < npx; q += 32) {
-                    int iv, ixv, iyv;
-                    fast_px(q, iv, ixv, iyv);
-                    pIw[q] = (short)iv; pIx[q] = (short)ixv; pIy[q] = (short)iyv;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int iv = descale(mid[i + 1], kWBits - 5);
+                    int ixv = descale(cs[i + 2] - cs[i], kWBits);
+                    int iyv = descale(3 * (rd[i] + rd[i + 2]) + 10 * rd[i + 1], kWBits);
+                    if (i >= nval[j]) { ixv = 0; iyv = 0; }
+                    set_px(j, i, iv, ixv, iyv);
                     sA11 += ixv * ixv; sA12 += ixv * iyv; sA22 += iyv * iyv;
                 }
             }
         } else {
-            // ---- border path: Scharr plane at (ipx..ipx+ww, ipy..ipy+wh), ZERO outside the image (calcScharrDeriv +
+            // ---- border path: Scharr plane at (ipx..ipx+WW, ipy..ipy+WH), ZERO outside the image (calcScharrDeriv +
             //      BORDER_CONSTANT), then bilinear on I, Ix, Iy exactly as OpenCV does
-            const int dpitch = ww + 1;
-            const int deriv_words = dpitch * (wh + 1);
-            {
-                const int dv = 32 / dpitch, du = 32 - dv * dpitch;
-                int v = lane / dpitch, u = lane - v * dpitch;
-                for (int d = lane; d < deriv_words; d += 32) {
-                    const int X = ipx + u, Y = ipy + v;
-                    uint32_t packed = 0;
-                    if (X >= 0 && X < L.w && Y >= 0 && Y < L.h) {
-                        const uint8_t* r0 = rb + v * rpitch + u;   // row Y-1, column X-1
-                        const uint8_t* r1 = r0 + rpitch;
-                        const uint8_t* r2 = r1 + rpitch;
-                        const int ix = 3 * ((int)r0[2] - (int)r0[0]) + 10 * ((int)r1[2] - (int)r1[0]) + 3 * ((int)r2[2] - (int)r2[0]);
-                        const int iy = 3 * ((int)r2[0] - (int)r0[0]) + 10 * ((int)r2[1] - (int)r0[1]) + 3 * ((int)r2[2] - (int)r0[2]);
-                        packed = ((uint32_t)ix & 0xffffu) | ((uint32_t)iy << 16);
-                    }
-                    plane[d] = (int)packed;
-                    u += du; v += dv;
-                    if (u >= dpitch) { u -= dpitch; ++v; }
+            constexpr int dpitch = WW + 1;
+            constexpr int deriv_words = dpitch * (WH + 1);
+            for (int d = lane; d < deriv_words; d += 32) {
+                const int v = d / dpitch, u = d - v * dpitch;
+                const int X = ipx + u, Y = ipy + v;
+                uint32_t packed = 0;
+                if (X >= 0 && X < L.w && Y >= 0 && Y < L.h) {
+                    const uint8_t* r0 = rbytes + v * G::RPI + u;   // row Y-1, column X-1
+                    const uint8_t* r1 = r0 + G::RPI;
+                    const uint8_t* r2 = r1 + G::RPI;
+                    const int ix = 3 * ((int)r0[2] - (int)r0[0]) + 10 * ((int)r1[2] - (int)r1[0]) + 3 * ((int)r2[2] - (int)r2[0]);
+                    const int iy = 3 * ((int)r2[0] - (int)r0[0]) + 10 * ((int)r2[1] - (int)r0[1]) + 3 * ((int)r2[2] - (int)r0[2]);
+                    packed = ((uint32_t)ix & 0xffffu) | ((uint32_t)iy << 16);
                 }
+                plane[d] = (int)packed;
             }
             __syncwarp();
-            auto slow_px = [&](int q, int& iv, int& ixv, int& iyv) {
-                const int y = q / ww, x = q - y * ww;
-                iv = descale(bilin(rb + (y + 1) * rpitch + x + 1, rpitch, w), kWBits - 5);
-                const int* dp = plane + q + y;   // y * dpitch + x
-                const int d00 = dp[0], d01 = dp[1], d10 = dp[dpitch], d11 = dp[dpitch + 1];
-                ixv = descale((int)(short)(d00 & 0xffff) * w.w00 + (int)(short)(d01 & 0xffff) * w.w01 +
-                                  (int)(short)(d10 & 0xffff) * w.w10 + (int)(short)(d11 & 0xffff) * w.w11, kWBits);
-                iyv = descale((d00 >> 16) * w.w00 + (d01 >> 16) * w.w01 + (d10 >> 16) * w.w10 + (d11 >> 16) * w.w11, kWBits);
-            };
-            if constexpr (FIXED) {
-#pragma unroll 1
-                for (int k = 0; k < NPL; ++k) {   // rare path: keep it small (not unrolled); dynamic register indexing
-                    const bool valid = lane + 32 * k < WW * WH;   // is avoided by the switch-free select chain below
-                    int iv, ixv, iyv;
-                    slow_px(valid ? lane + 32 * k : 0, iv, ixv, iyv);
-                    if (!valid) { ixv = 0; iyv = 0; }
 #pragma unroll
-                    for (int j = 0; j < NPL; ++j)
-                        if (j == k) { Iw[j] = iv; Ix[j] = ixv; Iy[j] = iyv; }
-                    sA11 += ixv * ixv; sA12 += ixv * iyv; sA22 += iyv * iyv;
-                }
-            } else {
-                for (int q = lane; q < npx; q += 32) {
-                    int iv, ixv, iyv;
-                    slow_px(q, iv, ixv, iyv);
-                    pIw[q] = (short)iv; pIx[q] = (short)ixv; pIy[q] = (short)iyv;
+            for (int j = 0; j < RPL; ++j) {
+                const int r = min(lane + 32 * j, G::RUNS - 1);
+                const int y = r / G::NSEG, x0 = 8 * (r - y * G::NSEG);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    int iv = 0, ixv = 0, iyv = 0;
+                    if (i < nval[j]) {
+                        const int x = x0 + i;
+                        iv = descale(bilin(rbytes + (y + 1) * G::RPI + x + 1, G::RPI, w), kWBits - 5);
+                        const int* dp = plane + y * dpitch + x;
+                        const int d00 = dp[0], d01 = dp[1], d10 = dp[dpitch], d11 = dp[dpitch + 1];
+                        ixv = descale((int)(short)(d00 & 0xffff) * w.w00 + (int)(short)(d01 & 0xffff) * w.w01 +
+                                          (int)(short)(d10 & 0xffff) * w.w10 + (int)(short)(d11 & 0xffff) * w.w11, kWBits);
+                        iyv = descale((d00 >> 16) * w.w00 + (d01 >> 16) * w.w01 + (d10 >> 16) * w.w10 + (d11 >> 16) * w.w11, kWBits);
+                    }
+                    set_px(j, i, iv, ixv, iyv);
                     sA11 += ixv * ixv; sA12 += ixv * iyv; sA22 += iyv * iyv;
                 }
             }
@@ -298,11 +339,7 @@ __global__ void __launch_bounds__(WARPS * 32) klt_kernel(const KltArgs a)
         const float A22 = __fmul_rn(__ll2float_rn(warp_sum_exact(sA22)), FLT_SCALE);
 
         float D = __fsub_rn(__fmul_rn(A11, A22), __fmul_rn(A12, A12));
-        const float dA = __fsub_rn(A11, A22);
-        const float minEig = __fdiv_rn(
-            __fsub_rn(__fadd_rn(A22, A11),
-                      __fsqrt_rn(__fadd_rn(__fmul_rn(dA, dA), __fmul_rn(__fmul_rn(4.f, A12), A12)))),
-            (float)(2 * ww * wh));
+        const float minEig = min_eig(A11, A12, A22, WW * WH);
         if (a.flags & SVO_GPU_LK_GET_MIN_EIGENVALS) er = minEig;
         if ((double)minEig < a.min_eig_threshold || D < FLT_EPSILON) {
             if (level == 0) st = 0;
@@ -310,23 +347,27 @@ __global__ void __launch_bounds__(WARPS * 32) klt_kernel(const KltArgs a)
         }
         D = __fdiv_rn(1.f, D);
 
-        // one pass over the window at the staged position of the next image: exact integer sums of
-        // diff*Ix, diff*Iy (Newton step) or |diff| (L1 residual)
-        auto window_pass = [&](const uint8_t* jb, int& s1, int& s2, bool l1) {
+        // one pass over the window at the staged position of the next image: exact integer sums of diff*Ix, diff*Iy
+        // (Newton step) or |diff| (L1 residual); diff = DESCALE(bilinear J, 9) - Iw, the rounding constant rides in the
+        // DP2A accumulator
+        auto window_pass = [&](int& s1, int& s2, auto l1_tag) {
+            constexpr bool L1 = decltype(l1_tag)::value;
+            const uint32_t wt = pack_weights(w.w00, w.w01), wb = pack_weights(w.w10, w.w11);
+            constexpr int RND = 1 << (kWBits - 6);
             s1 = 0; s2 = 0;
-            if constexpr (FIXED) {
 #pragma unroll
-                for (int k = 0; k < NPL; ++k) {
-                    const int diff = ((bilin(jb + offI[k], rpitch, w) + (1 << (kWBits - 6))) >> (kWBits - 5)) - Iw[k];
-                    if (l1) { if (lane + 32 * k < WW * WH) s1 += abs(diff); }
-                    else { s1 += diff * Ix[k]; s2 += diff * Iy[k]; }
-                }
-            } else {
-                for (int q = lane; q < npx; q += 32) {
-                    const int y = q / ww, x = q - y * ww;
-                    const int diff = descale(bilin(jb + y * rpitch + x, rpitch, w), kWBits - 5) - (int)pIw[q];
-                    if (l1) s1 += abs(diff);
-                    else { s1 += diff * (int)pIx[q]; s2 += diff * (int)pIy[q]; }
+            for (int j = 0; j < RPL; ++j) {
+                const RunRow top = load_run_row(jo[j]), bot = load_run_row(jo[j] + G::RPJ);
+                int v[8];
+                v[0] = run_px<0>(top, bot, wt, wb, RND) >> (kWBits - 5); v[1] = run_px<1>(top, bot, wt, wb, RND) >> (kWBits - 5);
+                v[2] = run_px<2>(top, bot, wt, wb, RND) >> (kWBits - 5); v[3] = run_px<3>(top, bot, wt, wb, RND) >> (kWBits - 5);
+                v[4] = run_px<4>(top, bot, wt, wb, RND) >> (kWBits - 5); v[5] = run_px<5>(top, bot, wt, wb, RND) >> (kWBits - 5);
+                v[6] = run_px<6>(top, bot, wt, wb, RND) >> (kWBits - 5); v[7] = run_px<7>(top, bot, wt, wb, RND) >> (kWBits - 5);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int diff = v[i] - Iw[j][i];
+                    if constexpr (L1) { if (i < nval[j]) s1 += abs(diff); }
+                    else { s1 += diff * get_ix(j, i); s2 += diff * get_iy(j, i); }   // invalid slots hold Ix = Iy = 0
                 }
             }
         };
@@ -336,17 +377,17 @@ __global__ void __launch_bounds__(WARPS * 32) klt_kernel(const KltArgs a)
         const uint8_t* Jorigin = Npyr + L.off;
         for (int j = 0; j < a.max_count; ++j) {
             const int inx = (int)floorf(nx), iny = (int)floorf(ny);
-            if (inx < -ww || inx >= L.w || iny < -wh || iny >= L.h) {
+            if (inx < -WW || inx >= L.w || iny < -WH || iny >= L.h) {
                 if (level == 0) st = 0;
                 break;
             }
             ++iters;
             w = bilinear_weights(__fsub_rn(nx, (float)inx), __fsub_rn(ny, (float)iny));
             __syncwarp();
-            ao = stage_region<IT_J>(region, Jorigin, L.pitch, inx, iny, wh + 1, nwords, st_r0, st_c0, rpi);
+            stage_shifted<G::JROWS, G::RPJ>(sJ_dst, Jorigin + (long long)(iny + sJ_r) * L.pitch + ((inx & ~3) + 4 * sJ_c), L.pitch, inx);
             __syncwarp();
             int sb1, sb2;
-            window_pass(rbytes + ao, sb1, sb2, false);
+            window_pass(sb1, sb2, std::false_type{});
             const float b1 = __fmul_rn(__ll2float_rn(warp_sum_exact(sb1)), FLT_SCALE);
             const float b2 = __fmul_rn(__ll2float_rn(warp_sum_exact(sb2)), FLT_SCALE);
             const float dx = __fmul_rn(__fsub_rn(__fmul_rn(A12, b2), __fmul_rn(A22, b1)), D);
@@ -366,17 +407,17 @@ __global__ void __launch_bounds__(WARPS * 32) klt_kernel(const KltArgs a)
         if (st && level == 0 && (a.flags & SVO_GPU_LK_GET_MIN_EIGENVALS) == 0) {
             const float qx = __fsub_rn(ox, halfx), qy = __fsub_rn(oy, halfy);
             const int iqx = (int)floorf(qx), iqy = (int)floorf(qy);
-            if (iqx < -ww || iqx >= L.w || iqy < -wh || iqy >= L.h) {
+            if (iqx < -WW || iqx >= L.w || iqy < -WH || iqy >= L.h) {
                 st = 0;
                 continue;
             }
             w = bilinear_weights(__fsub_rn(qx, (float)iqx), __fsub_rn(qy, (float)iqy));
             __syncwarp();
-            ao = stage_region<IT_J>(region, Jorigin, L.pitch, iqx, iqy, wh + 1, nwords, st_r0, st_c0, rpi);
+            stage_shifted<G::JROWS, G::RPJ>(sJ_dst, Jorigin + (long long)(iqy + sJ_r) * L.pitch + ((iqx & ~3) + 4 * sJ_c), L.pitch, iqx);
             __syncwarp();
             int serr, unused;
-            window_pass(rbytes + ao, serr, unused, true);
-            er = __fdiv_rn(__fmul_rn(__ll2float_rn(warp_sum_exact(serr)), 1.f), (float)(32 * ww * wh));
+            window_pass(serr, unused, std::true_type{});
+            er = __fdiv_rn(__fmul_rn(__ll2float_rn(warp_sum_exact(serr)), 1.f), (float)(32 * WW * WH));
         }
     }
 
@@ -388,11 +429,11 @@ __global__ void __launch_bounds__(WARPS * 32) klt_kernel(const KltArgs a)
     }
 }
 
-template <int WW, int WH, int WARPS>
-void launch_fixed(cudaStream_t st, const KltArgs& a, int batch)
+template <int WW, int WH, int WARPS, bool PACKG>
+void launch_run(cudaStream_t st, const KltArgs& a, int batch)
 {
     dim3 grid((a.n_max + WARPS - 1) / WARPS, batch);
-    klt_kernel<WW, WH, WARPS><<<grid, WARPS * 32, 0, st>>>(a);
+    klt_run_kernel<WW, WH, WARPS, PACKG><<<grid, WARPS * 32, 0, st>>>(a);
 }
 
 }  // namespace
@@ -400,18 +441,10 @@ void launch_fixed(cudaStream_t st, const KltArgs& a, int batch)
 void launch_klt(cudaStream_t st, const KltArgs& a, int batch, long long* launches)
 {
     if (a.n_max <= 0) return;
-    if (a.win_w == 21 && a.win_h == 21) launch_fixed<21, 21, 8>(st, a, batch);
-    else if (a.win_w == 11 && a.win_h == 11) launch_fixed<11, 11, 8>(st, a, batch);
-    else if (a.win_w == 31 && a.win_h == 31) launch_fixed<31, 31, 4>(st, a, batch);
-    else {
-        constexpr int WARPS = 4;
-        const int ww = a.win_w, wh = a.win_h;
-        const int words = (wh + 3) * ((ww + 9) >> 2) + (ww + 2) * (wh + 2) + (3 * ww * wh + 1) / 2;
-        const size_t bytes = (size_t)WARPS * words * 4;
-        cudaFuncSetAttribute(klt_kernel<0, 0, WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
-        dim3 grid((a.n_max + WARPS - 1) / WARPS, batch);
-        klt_kernel<0, 0, WARPS><<<grid, WARPS * 32, bytes, st>>>(a);
-    }
+    if (a.win_w == 21 && a.win_h == 21) launch_run<21, 21, 8, false>(st, a, batch);
+    else if (a.win_w == 11 && a.win_h == 11) launch_run<11, 11, 8, false>(st, a, batch);
+    else if (a.win_w == 31 && a.win_h == 31) launch_run<31, 31, 4, true>(st, a, batch);
+    else launch_klt_generic(st, a, batch);
     if (launches) ++*launches;
 }
 

@@ -202,6 +202,23 @@ def test_klt_vs_cv2(ctx, oracle, c1_frames, mode):
     assert np.allclose(er[both], cer[both], rtol=5e-3, atol=1e-5)
 
 
+def test_klt_negative_corner_weight(ctx, oracle, small_frames):
+    """Fractions of ~0.6 / 2^14 round iw00, iw01, iw10 all upwards, so iw11 = 2^14 - (their sum) = -1: the bilinear weights
+    must be treated as signed (a DP2A with unsigned 16-bit weights would read 65535)."""
+    a, b = small_frames
+    base = np.floor(_lk_points(oracle, a, 200)[:200])
+    pts = (base + np.float32(3.8e-5)).astype(np.float32)
+    assert np.all(pts != base)
+    for mode in MODES[:2]:
+        ctx.upload(0, a)
+        ctx.upload(1, b)
+        ctx.build_pyramid(0, mode["win"], mode["max_level"])
+        ctx.build_pyramid(1, mode["win"], mode["max_level"])
+        nxy, st, er = ctx.klt(0, 1, pts, **dict(mode, max_level=0))
+        oxy, ost, oer = oracle.orc_klt(a, b, pts, **dict(mode, max_level=0))
+        assert np.array_equal(st, ost) and np.array_equal(nxy, oxy) and np.array_equal(er, oer)
+
+
 def test_klt_known_answers(ctx, oracle, c1_frames):
     a, _ = c1_frames
     pts = _lk_points(oracle, a, 500)[:500]
