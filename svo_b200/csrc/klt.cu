@@ -40,8 +40,15 @@ struct RunGeo {
     static constexpr int NSEG = WW / 8 + 1;            // 8-pixel runs per window row (the last one partial)
     static constexpr int RUNS = WH * NSEG;
     static constexpr int RPL = (RUNS + 31) / 32;       // runs per lane
-    static constexpr int RPJ = 8 * NSEG;               // bytes per staged row of the next image (needs WW + 1)
-    static constexpr int JROWS = WH + 1;
+    // next-image region: the (WW+1) x (WH+1) window plus a margin of MJ pixels on every side, staged UNSHIFTED (word
+    // aligned) once per level; the Newton iterations move the window inside it and only re-stage when they leave it
+    static constexpr int MJ = 3;
+    static constexpr int PJ0 = (WW + 1 + 3 + 2 * MJ + 3) & ~3;
+    static constexpr int PJ = (PJ0 / 4) % 2 == 0 ? PJ0 + 4 : PJ0;   // bytes per row; an odd word count spreads the banks
+    static constexpr int DXMAX = PJ - 1 - WW, DYMAX = 2 * MJ;       // legal window offsets inside the region
+    static constexpr int OWJ = PJ / 4, RPPJ = 32 / OWJ;
+    static constexpr int PASSJ = (WH + 1 + 2 * MJ + RPPJ - 1) / RPPJ;
+    static constexpr int JREGION_WORDS = (PASSJ * RPPJ * OWJ + 4 + 3) & ~3;
     static constexpr int NSEGB = (WW + 2) / 8 + 1;     // runs per row of the B plane (WW + 2 values per row)
     static constexpr int RPI = 8 * NSEGB;              // bytes per staged row of the previous image (needs WW + 3)
     static constexpr int IROWS = WH + 3;
@@ -51,10 +58,9 @@ struct RunGeo {
     static constexpr int RPLB = (RUNSB + 31) / 32;
     // staging works in whole passes of 32 / (RP/4) rows (no predicates): the region holds the rounded-up row counts
     static constexpr int IROWS_ST = (IROWS + 32 / (RPI / 4) - 1) / (32 / (RPI / 4)) * (32 / (RPI / 4));
-    static constexpr int JROWS_ST = (JROWS + 32 / (RPJ / 4) - 1) / (32 / (RPJ / 4)) * (32 / (RPJ / 4));
-    static constexpr int REGION_WORDS = ((IROWS_ST * RPI > JROWS_ST * RPJ ? IROWS_ST * RPI : JROWS_ST * RPJ) / 4 + 4 + 3) & ~3;
+    static constexpr int REGION_WORDS = (IROWS_ST * RPI / 4 + 4 + 3) & ~3;
     static constexpr int PLANE_WORDS = (PROWS * BP + 8 + 3) & ~3;
-    static constexpr int WARP_WORDS = REGION_WORDS + PLANE_WORDS;
+    static constexpr int WARP_WORDS = REGION_WORDS + PLANE_WORDS + JREGION_WORDS;
 };
 
 // The eight (byte i, byte i+1) pairs of a run, as DP2A operands: with w0 = bytes 0..3, w1 = 4..7, w2 = 8.. of the run,
@@ -103,6 +109,24 @@ __device__ __forceinline__ RunRow load_run_row(uint32_t addr)
     r.s1 = __funnelshift_r(a.y, b, 8);
     return r;
 }
+
+// same for a run that starts `sh / 8` bytes into the word at addr (sh = 0, 8, 16, 24; warp-uniform)
+__device__ __forceinline__ RunRow load_run_row_unaligned(uint32_t addr, int sh)
+{
+    const uint32_t a = lds32(addr), b = lds32(addr + 4), c = lds32(addr + 8);
+    RunRow r;
+    r.w0 = __funnelshift_r(a, b, sh);
+    r.w1 = __funnelshift_r(b, c, sh);
+    r.s0 = __funnelshift_rc(a, b, sh + 8);
+    r.s1 = __funnelshift_rc(b, c, sh + 8);
+    return r;
+}
+
+__device__ __forceinline__ void cp_async4(uint32_t dst, const void* src)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // d = c + a.lo16 * b.byte[0 or 2] + a.hi16 * b.byte[1 or 3]: SIGNED 16-bit weights (iw11 = 2^14 - iw00 - iw01 - iw10 can
 // come out as -1 when the three roundings all go up), UNSIGNED 8-bit pixels.
@@ -170,12 +194,13 @@ __global__ void __launch_bounds__(WARPS * 32) klt_run_kernel(const KltArgs a)
     const uint8_t* rbytes = reinterpret_cast<const uint8_t*>(region);
 
     // ---- per-lane constants: staging maps, and for each owned run its offsets and number of valid pixels
-    constexpr int OWI = G::RPI / 4, OWJ = G::RPJ / 4;
+    constexpr int OWI = G::RPI / 4, OWJ = G::OWJ;
     const uint32_t region_sa = (uint32_t)__cvta_generic_to_shared(region);   // 32-bit shared-window addresses
     const uint32_t plane_sa = (uint32_t)__cvta_generic_to_shared(plane);
     const int sI_r = min(lane / OWI, 32 / OWI - 1), sI_c = lane % OWI;       // staging maps: lane -> (row, word) of a pass;
-    const int sJ_r = min(lane / OWJ, 32 / OWJ - 1), sJ_c = lane % OWJ;       // spare lanes repeat a word of the last row
-    const uint32_t sI_dst = region_sa + 4 * (sI_r * OWI + sI_c), sJ_dst = region_sa + 4 * (sJ_r * OWJ + sJ_c);
+    const int sJ_r = min(lane / OWJ, G::RPPJ - 1), sJ_c = lane % OWJ;        // spare lanes repeat a word of the last row
+    const uint32_t jregion_sa = plane_sa + 4 * G::PLANE_WORDS;
+    const uint32_t sI_dst = region_sa + 4 * (sI_r * OWI + sI_c), sJ_dst = jregion_sa + 4 * (sJ_r * OWJ + sJ_c);
     uint32_t jo[RPL], po[RPL];
     int nval[RPL];
 #pragma unroll
@@ -183,7 +208,7 @@ __global__ void __launch_bounds__(WARPS * 32) klt_run_kernel(const KltArgs a)
         const int r = lane + 32 * j;
         const int rr = min(r, G::RUNS - 1);
         const int y = rr / G::NSEG, seg = rr - y * G::NSEG;
-        jo[j] = region_sa + 8 * rr;     // shared address of the run in the staged next-image region (rows RPJ = 8 NSEG apart)
+        jo[j] = jregion_sa + y * G::PJ + 8 * seg;    // shared address of the run when the window sits at (0, 0) of the region
         po[j] = plane_sa + 4 * (y * BP + 8 * seg);   // shared address of plane element (x, y), x = the run's first pixel
         nval[j] = r < G::RUNS ? min(8, WW - 8 * seg) : 0;
     }
@@ -227,8 +252,29 @@ __global__ void __launch_bounds__(WARPS * 32) klt_run_kernel(const KltArgs a)
         }
         BiW w = bilinear_weights(__fsub_rn(px, (float)ipx), __fsub_rn(py, (float)ipy));
 
+        // ---- next image: start the asynchronous copy of the window region (+ margin) around the initial guess now, so
+        //      that its L2 latency hides behind the patch set-up below
+        nx = __fsub_rn(nx, halfx); ny = __fsub_rn(ny, halfy);
+        const uint8_t* Jorigin = Npyr + L.off;
+        int sx0 = 0, sy0 = 0;      // image coordinates of region byte (0, 0)
+        bool jstaged = false;
+        auto stage_j = [&](int inx, int iny) {
+            sx0 = (inx - G::MJ) & ~3;
+            sy0 = iny - G::MJ;
+            const uint8_t* src = Jorigin + (long long)(sy0 + sJ_r) * L.pitch + (sx0 + 4 * sJ_c);
+#pragma unroll
+            for (int k = 0; k < G::PASSJ; ++k)
+                cp_async4(sJ_dst + k * G::RPPJ * G::PJ, src + (long long)(k * G::RPPJ) * L.pitch);
+            jstaged = true;
+        };
+        cp_async_wait_all();   // a copy started at a level that was then skipped may still be in flight
+        __syncwarp();          // and every lane is done reading the previous level's regions
+        {
+            const int inx = (int)floorf(nx), iny = (int)floorf(ny);
+            if (inx >= -WW && inx < L.w && iny >= -WH && iny < L.h) stage_j(inx, iny);
+        }
+
         // ---- stage the (WW+3) x (WH+3) region of I whose top-left is (ipx-1, ipy-1); staged byte (u, v) = I(ipx-1+u, ipy-1+v)
-        __syncwarp();
         {
             const int x0 = ipx - 1;
             const uint8_t* src0 = Ppyr + L.off + (long long)(ipy - 1 + sI_r) * L.pitch + ((x0 & ~3) + 4 * sI_c);
@@ -350,14 +396,16 @@ __global__ void __launch_bounds__(WARPS * 32) klt_run_kernel(const KltArgs a)
         // one pass over the window at the staged position of the next image: exact integer sums of diff*Ix, diff*Iy
         // (Newton step) or |diff| (L1 residual); diff = DESCALE(bilinear J, 9) - Iw, the rounding constant rides in the
         // DP2A accumulator
-        auto window_pass = [&](int& s1, int& s2, auto l1_tag) {
+        auto window_pass = [&](int dx, int dy, int& s1, int& s2, auto l1_tag) {
             constexpr bool L1 = decltype(l1_tag)::value;
+            const uint32_t uoff = (uint32_t)(dy * G::PJ + (dx & ~3));   // warp-uniform: window origin inside the region
+            const int sh = 8 * (dx & 3);
             const uint32_t wt = pack_weights(w.w00, w.w01), wb = pack_weights(w.w10, w.w11);
             constexpr int RND = 1 << (kWBits - 6);
             s1 = 0; s2 = 0;
 #pragma unroll
             for (int j = 0; j < RPL; ++j) {
-                const RunRow top = load_run_row(jo[j]), bot = load_run_row(jo[j] + G::RPJ);
+                const RunRow top = load_run_row_unaligned(jo[j] + uoff, sh), bot = load_run_row_unaligned(jo[j] + uoff + G::PJ, sh);
                 int v[8];
                 v[0] = run_px<0>(top, bot, wt, wb, RND) >> (kWBits - 5); v[1] = run_px<1>(top, bot, wt, wb, RND) >> (kWBits - 5);
                 v[2] = run_px<2>(top, bot, wt, wb, RND) >> (kWBits - 5); v[3] = run_px<3>(top, bot, wt, wb, RND) >> (kWBits - 5);
@@ -372,9 +420,21 @@ __global__ void __launch_bounds__(WARPS * 32) klt_run_kernel(const KltArgs a)
             }
         };
 
-        nx = __fsub_rn(nx, halfx); ny = __fsub_rn(ny, halfy);
+        // window origin inside the staged region; re-stages (rare) when the window has left it
+        auto locate = [&](int inx, int iny, int& dx, int& dy) {
+            dx = inx - sx0; dy = iny - sy0;
+            if (!jstaged || (unsigned)dx > (unsigned)G::DXMAX || (unsigned)dy > (unsigned)G::DYMAX) {   // warp-uniform
+                __syncwarp();
+                cp_async_wait_all();
+                stage_j(inx, iny);
+                cp_async_wait_all();
+                __syncwarp();
+                dx = inx - sx0; dy = iny - sy0;
+            }
+        };
+        cp_async_wait_all();
+        __syncwarp();
         float pdx = 0.f, pdy = 0.f;
-        const uint8_t* Jorigin = Npyr + L.off;
         for (int j = 0; j < a.max_count; ++j) {
             const int inx = (int)floorf(nx), iny = (int)floorf(ny);
             if (inx < -WW || inx >= L.w || iny < -WH || iny >= L.h) {
@@ -383,11 +443,9 @@ __global__ void __launch_bounds__(WARPS * 32) klt_run_kernel(const KltArgs a)
             }
             ++iters;
             w = bilinear_weights(__fsub_rn(nx, (float)inx), __fsub_rn(ny, (float)iny));
-            __syncwarp();
-            stage_shifted<G::JROWS, G::RPJ>(sJ_dst, Jorigin + (long long)(iny + sJ_r) * L.pitch + ((inx & ~3) + 4 * sJ_c), L.pitch, inx);
-            __syncwarp();
-            int sb1, sb2;
-            window_pass(sb1, sb2, std::false_type{});
+            int wdx, wdy, sb1, sb2;
+            locate(inx, iny, wdx, wdy);
+            window_pass(wdx, wdy, sb1, sb2, std::false_type{});
             const float b1 = __fmul_rn(__ll2float_rn(warp_sum_exact(sb1)), FLT_SCALE);
             const float b2 = __fmul_rn(__ll2float_rn(warp_sum_exact(sb2)), FLT_SCALE);
             const float dx = __fmul_rn(__fsub_rn(__fmul_rn(A12, b2), __fmul_rn(A22, b1)), D);
@@ -395,7 +453,8 @@ __global__ void __launch_bounds__(WARPS * 32) klt_run_kernel(const KltArgs a)
             nx = __fadd_rn(nx, dx); ny = __fadd_rn(ny, dy);
             ox = __fadd_rn(nx, halfx); oy = __fadd_rn(ny, halfy);
             if (__dadd_rn(__dmul_rn((double)dx, (double)dx), __dmul_rn((double)dy, (double)dy)) <= a.eps2) break;
-            if (j > 0 && (double)fabsf(__fadd_rn(dx, pdx)) < 0.01 && (double)fabsf(__fadd_rn(dy, pdy)) < 0.01) {
+            // |d + dprev| < 0.01 (a double in OpenCV): 0.01f is the largest float below 0.01, so the float test `<= 0.01f` is the same
+            if (j > 0 && fabsf(__fadd_rn(dx, pdx)) <= 0.01f && fabsf(__fadd_rn(dy, pdy)) <= 0.01f) {
                 ox = __fsub_rn(ox, __fmul_rn(dx, 0.5f));
                 oy = __fsub_rn(oy, __fmul_rn(dy, 0.5f));
                 break;
@@ -412,11 +471,9 @@ __global__ void __launch_bounds__(WARPS * 32) klt_run_kernel(const KltArgs a)
                 continue;
             }
             w = bilinear_weights(__fsub_rn(qx, (float)iqx), __fsub_rn(qy, (float)iqy));
-            __syncwarp();
-            stage_shifted<G::JROWS, G::RPJ>(sJ_dst, Jorigin + (long long)(iqy + sJ_r) * L.pitch + ((iqx & ~3) + 4 * sJ_c), L.pitch, iqx);
-            __syncwarp();
-            int serr, unused;
-            window_pass(serr, unused, std::true_type{});
+            int wdx, wdy, serr, unused;
+            locate(iqx, iqy, wdx, wdy);
+            window_pass(wdx, wdy, serr, unused, std::true_type{});
             er = __fdiv_rn(__fmul_rn(__ll2float_rn(warp_sum_exact(serr)), 1.f), (float)(32 * WW * WH));
         }
     }
