@@ -9,7 +9,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libsvo_gpu.so")
+# SVO_GPU_LIB selects another build of the same library (kernel tuning variants); never a different implementation
+LIB_PATH = os.environ.get("SVO_GPU_LIB") or os.path.join(_HERE, "lib", "libsvo_gpu.so")
 
 OK, E_ARG, E_CAPACITY, E_CUDA, E_UNSUPPORTED, E_STATE = 0, -1, -2, -3, -4, -5
 NUM_SLOTS = 4

@@ -174,8 +174,8 @@ __device__ __forceinline__ void stage_shifted(uint32_t dst0, const uint8_t* __re
     for (int k = 0; k < PASSES; ++k) sts32(dst0 + k * RPP * RP, __funnelshift_r(lo[k], hi[k], sh));
 }
 
-template <int WW, int WH, int WARPS, bool PACKG>
-__global__ void __launch_bounds__(WARPS * 32) klt_run_kernel(const KltArgs a)
+template <int WW, int WH, int WARPS, bool PACKG, int MINB>
+__global__ void __launch_bounds__(WARPS * 32, MINB) klt_run_kernel(const KltArgs a)
 {
     using G = RunGeo<WW, WH>;
     constexpr int RPL = G::RPL, BP = G::BP;
@@ -380,9 +380,9 @@ __global__ void __launch_bounds__(WARPS * 32) klt_run_kernel(const KltArgs a)
                 }
             }
         }
-        const float A11 = __fmul_rn(__ll2float_rn(warp_sum_exact(sA11)), FLT_SCALE);
-        const float A12 = __fmul_rn(__ll2float_rn(warp_sum_exact(sA12)), FLT_SCALE);
-        const float A22 = __fmul_rn(__ll2float_rn(warp_sum_exact(sA22)), FLT_SCALE);
+        const float A11 = __fmul_rn(warp_sum_exact_f(sA11), FLT_SCALE);
+        const float A12 = __fmul_rn(warp_sum_exact_f(sA12), FLT_SCALE);
+        const float A22 = __fmul_rn(warp_sum_exact_f(sA22), FLT_SCALE);
 
         float D = __fsub_rn(__fmul_rn(A11, A22), __fmul_rn(A12, A12));
         const float minEig = min_eig(A11, A12, A22, WW * WH);
@@ -446,8 +446,8 @@ __global__ void __launch_bounds__(WARPS * 32) klt_run_kernel(const KltArgs a)
             int wdx, wdy, sb1, sb2;
             locate(inx, iny, wdx, wdy);
             window_pass(wdx, wdy, sb1, sb2, std::false_type{});
-            const float b1 = __fmul_rn(__ll2float_rn(warp_sum_exact(sb1)), FLT_SCALE);
-            const float b2 = __fmul_rn(__ll2float_rn(warp_sum_exact(sb2)), FLT_SCALE);
+            const float b1 = __fmul_rn(warp_sum_exact_f(sb1), FLT_SCALE);
+            const float b2 = __fmul_rn(warp_sum_exact_f(sb2), FLT_SCALE);
             const float dx = __fmul_rn(__fsub_rn(__fmul_rn(A12, b2), __fmul_rn(A22, b1)), D);
             const float dy = __fmul_rn(__fsub_rn(__fmul_rn(A12, b1), __fmul_rn(A11, b2)), D);
             nx = __fadd_rn(nx, dx); ny = __fadd_rn(ny, dy);
@@ -474,7 +474,7 @@ __global__ void __launch_bounds__(WARPS * 32) klt_run_kernel(const KltArgs a)
             int wdx, wdy, serr, unused;
             locate(iqx, iqy, wdx, wdy);
             window_pass(wdx, wdy, serr, unused, std::true_type{});
-            er = __fdiv_rn(__fmul_rn(__ll2float_rn(warp_sum_exact(serr)), 1.f), (float)(32 * WW * WH));
+            er = __fdiv_rn(__fmul_rn(warp_sum_exact_f(serr), 1.f), (float)(32 * WW * WH));
         }
     }
 
@@ -486,21 +486,32 @@ __global__ void __launch_bounds__(WARPS * 32) klt_run_kernel(const KltArgs a)
     }
 }
 
-template <int WW, int WH, int WARPS, bool PACKG>
+template <int WW, int WH, int WARPS, bool PACKG, int MINB>
 void launch_run(cudaStream_t st, const KltArgs& a, int batch)
 {
     dim3 grid((a.n_max + WARPS - 1) / WARPS, batch);
-    klt_run_kernel<WW, WH, WARPS, PACKG><<<grid, WARPS * 32, 0, st>>>(a);
+    klt_run_kernel<WW, WH, WARPS, PACKG, MINB><<<grid, WARPS * 32, 0, st>>>(a);
 }
+
+// tuning knobs of the 21x21 instantiation (warps per CTA, packed gradients, minimum CTAs per SM -> register cap)
+#ifndef KLT21_WARPS
+#define KLT21_WARPS 4
+#endif
+#ifndef KLT21_PACKG
+#define KLT21_PACKG false
+#endif
+#ifndef KLT21_MINB
+#define KLT21_MINB 5
+#endif
 
 }  // namespace
 
 void launch_klt(cudaStream_t st, const KltArgs& a, int batch, long long* launches)
 {
     if (a.n_max <= 0) return;
-    if (a.win_w == 21 && a.win_h == 21) launch_run<21, 21, 8, false>(st, a, batch);
-    else if (a.win_w == 11 && a.win_h == 11) launch_run<11, 11, 8, false>(st, a, batch);
-    else if (a.win_w == 31 && a.win_h == 31) launch_run<31, 31, 4, true>(st, a, batch);
+    if (a.win_w == 21 && a.win_h == 21) launch_run<21, 21, KLT21_WARPS, KLT21_PACKG, KLT21_MINB>(st, a, batch);
+    else if (a.win_w == 11 && a.win_h == 11) launch_run<11, 11, 8, false, 2>(st, a, batch);
+    else if (a.win_w == 31 && a.win_h == 31) launch_run<31, 31, 4, true, 1>(st, a, batch);
     else launch_klt_generic(st, a, batch);
     if (launches) ++*launches;
 }

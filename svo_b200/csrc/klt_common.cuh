@@ -36,6 +36,15 @@ __device__ __forceinline__ long long warp_sum_exact(int v)
     return ((long long)hi << 16) + (long long)lo;
 }
 
+// the same sum as a correctly rounded float32, i.e. (float)(exact 64-bit total): both partial sums are below 2^22 in
+// magnitude, so hi * 65536 and lo are exact floats and the single rounding happens in the final addition
+__device__ __forceinline__ float warp_sum_exact_f(int v)
+{
+    const unsigned lo = __reduce_add_sync(kFull, (unsigned)(v & 0xffff));
+    const int hi = __reduce_add_sync(kFull, v >> 16);
+    return __fadd_rn(__fmul_rn(__int2float_rn(hi), 65536.f), __uint2float_rn(lo));
+}
+
 // unrounded bilinear sample at byte pointer p (row pitch rp)
 __device__ __forceinline__ int bilin(const uint8_t* __restrict__ p, int rp, const BiW& w)
 {
