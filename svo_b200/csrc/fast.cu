@@ -9,8 +9,8 @@
 //   keypoints come out in raster order (y, then x); points whose mask pixel is 0 are dropped afterwards.
 //
 // Two kernels, both deterministic (bit-exact list equality needs ordered compaction, so no atomics decide positions):
-//   fast_tile_kernel   one CTA per 64x16 tile: image tile + 4 px halo staged in shared memory, segment test on the
-//                      (64+2)x(16+2) score region, dense second pass over the surviving corners for the score, NMS, and
+//   fast_tile_kernel   one CTA per 128x32 tile: image tile + 4 px halo staged in shared memory, packed pre-test, segment test on the
+//                      candidates over the (128+2)x(32+2) score region, dense pass over the surviving corners for the score, NMS, and
 //                      a per-(row, tile) segment of kept keypoints written in x order via warp ballots.
 //   fast_gather_kernel one CTA per image row: offset = keypoints in all earlier rows (sum of the per-row counters) +
 //                      segments to the left; copies the segments to the final (x, y, response) list.
@@ -21,9 +21,11 @@ namespace svo {
 namespace {
 
 constexpr int TW = kFastTW, TH = kFastTH;
-constexpr int RW = TW + 8, RH = TH + 8;   // staged image region (halo 3 for the ring + 1 for the NMS neighbours)
-constexpr int SW = TW + 2, SH = TH + 2;   // score region
+constexpr int RW = TW + 8, RH = TH + 8;   // staged image region (halo 3 for the ring + 1 for the NMS neighbours), origin (x0-4, y0-4)
+constexpr int RWW = RW / 4;               // words per staged row
+constexpr int SW = TW + 2, SH = TH + 2;   // score region, origin (x0-1, y0-1) = staged (3, 3)
 constexpr int SWP = SW + 2;               // padded score row
+constexpr int NG = RWW;                   // 4-pixel groups per score row (staged columns 4g .. 4g+3)
 
 // ring offsets in the staged tile (row pitch RW), order of OpenCV's pixel[] table
 __device__ __forceinline__ constexpr int ring_off(int k)
@@ -50,6 +52,25 @@ __device__ __forceinline__ bool run9(uint32_t m)
 
 __device__ __forceinline__ int min3(int a, int b, int c) { return min(min(a, b), c); }
 __device__ __forceinline__ int max3(int a, int b, int c) { return max(max(a, b), c); }
+
+// ---- packed pre-test: four horizontally adjacent pixels per thread, two per 32-bit register (16-bit fields).
+// For a field holding ring value r and centre c:  (0x8000 - (c+t+1)) + r has bit 15 set iff r > c + t  (brighter),
+//                                                  (0x8000 + c-t-1) - r has bit 15 set iff r < c - t  (darker);
+// every field stays inside [0x7DFF, 0x80FE], so no carry or borrow crosses the fields.
+struct PreAcc {
+    uint32_t be, bo, de, dout;   // running AND over opposite pairs of (flag_k | flag_k+8): bright/dark x even/odd pixels
+};
+
+__device__ __forceinline__ void pre_pair(PreAcc& acc, uint32_t wa, uint32_t wb, uint32_t k1e, uint32_t k1o, uint32_t k2e,
+                                         uint32_t k2o, bool first)
+{
+    const uint32_t ae = __byte_perm(wa, 0, 0x4240), ao = __byte_perm(wa, 0, 0x4341);   // bytes (0,2) / (1,3) as 16-bit fields
+    const uint32_t be = __byte_perm(wb, 0, 0x4240), bo = __byte_perm(wb, 0, 0x4341);
+    const uint32_t bre = (ae + k1e) | (be + k1e), bro = (ao + k1o) | (bo + k1o);
+    const uint32_t dke = (k2e - ae) | (k2e - be), dko = (k2o - ao) | (k2o - bo);
+    if (first) { acc.be = bre; acc.bo = bro; acc.de = dke; acc.dout = dko; }
+    else { acc.be &= bre; acc.bo &= bro; acc.de &= dke; acc.dout &= dko; }
+}
 
 // cornerScore<16>: best = max over arcs of min(d) and min(-d).
 // Both polarities are computed as minima (of d and of e = -d).  Writing the bright side as -max(d) made nvcc 12.9 emit
@@ -84,23 +105,26 @@ __global__ void __launch_bounds__(256) fast_tile_kernel(const uint8_t* __restric
                                                         int w, int h, int t, int nms, const uint8_t* __restrict__ mask,
                                                         size_t mask_pitch, size_t mask_lane, FastBufs fb, int ntx)
 {
-    __shared__ __align__(16) uint8_t img[RH * RW];
+    __shared__ __align__(16) uint32_t simg_pad[RH * RWW + 2];   // one pad word on each side: the pre-test reads words g-1, g+1
     __shared__ uint8_t best[SH * SWP];
-    __shared__ uint16_t cand[SH * SW];
-    __shared__ int ncand;
+    __shared__ uint16_t cand[SH * SW];     // pixels that pass the packed pre-test
+    __shared__ uint16_t corner[SH * SW];   // pixels that pass the full segment test
+    __shared__ int ncand, ncorner;
 
+    uint32_t* simg = simg_pad + 1;
+    const uint8_t* img = reinterpret_cast<const uint8_t*>(simg);
     const int tid = threadIdx.x;
     const int x0 = blockIdx.x * TW, y0 = blockIdx.y * TH;
     const int lane_id = blockIdx.z;
     const uint8_t* src = raw + (size_t)lane_id * raw_lane;
 
-    if (tid == 0) ncand = 0;
+    if (tid == 0) { ncand = 0; ncorner = 0; simg_pad[0] = 0; simg_pad[RH * RWW + 1] = 0; }
 
     // ---- stage the (TW+8) x (TH+8) region; coordinates are clamped to the image (clamped pixels are never used by a
     //      valid candidate: those sit at least 3 px inside the image)
     const bool aligned = ((reinterpret_cast<uintptr_t>(src) | raw_pitch) & 3) == 0;
-    for (int i = tid; i < RH * (RW / 4); i += 256) {
-        const int r = i / (RW / 4), cw = i - r * (RW / 4);
+    for (int i = tid; i < RH * RWW; i += 256) {
+        const int r = i / RWW, cw = i - r * RWW;
         const int gy = min(max(y0 - 4 + r, 0), h - 1);
         const int gx = x0 - 4 + cw * 4;
         const uint8_t* row = src + (size_t)gy * raw_pitch;
@@ -112,65 +136,90 @@ __global__ void __launch_bounds__(256) fast_tile_kernel(const uint8_t* __restric
 #pragma unroll
             for (int b = 0; b < 4; ++b) v |= (uint32_t)__ldg(row + min(max(gx + b, 0), w - 1)) << (8 * b);
         }
-        reinterpret_cast<uint32_t*>(img)[r * (RW / 4) + cw] = v;
+        simg[i] = v;
     }
     for (int i = tid; i < SH * SWP; i += 256) best[i] = 0;
     __syncthreads();
 
-    // ---- pass 1: segment test on the score region, corners appended to a shared candidate list
-    const uint32_t tt = (uint32_t)t;
-    for (int p = tid; p < SH * SW; p += 256) {
-        const int sy = p / SW, sx = p - sy * SW;
-        const int gx = x0 - 1 + sx, gy = y0 - 1 + sy;
-        bool is_corner = false;
-        if (gx >= 3 && gx <= w - 4 && gy >= 3 && gy <= h - 4) {
-            const uint8_t* c = img + (sy + 3) * RW + sx + 3;
-            const uint32_t cv = c[0];
-            const uint32_t C = (0x8000u - (cv - tt)) + ((cv + tt + 0x8000u) << 16);
-            // compass points first: any 9-arc holds at least 2 of the ring pixels 0, 4, 8, 12
-            const uint32_t f0 = classify(c[ring_off(0)], C), f4 = classify(c[ring_off(4)], C);
-            const uint32_t f8 = classify(c[ring_off(8)], C), f12 = classify(c[ring_off(12)], C);
-            const uint32_t nd = ((f0 >> 15) & 1) + ((f4 >> 15) & 1) + ((f8 >> 15) & 1) + ((f12 >> 15) & 1);
-            const uint32_t nb = (f0 >> 31) + (f4 >> 31) + (f8 >> 31) + (f12 >> 31);
-            if (nd <= 2 || nb <= 2) {   // at least 2 compass pixels darker, or at least 2 brighter
-                uint32_t acc = ((f0 >> 15) & 0x00010001u) | (((f4 >> 11)) & 0x00100010u) |
-                               ((f8 >> 7) & 0x01000100u) | ((f12 >> 3) & 0x10001000u);
+    // ---- pass 0: packed pre-test on 4-pixel groups.  A 9-arc holds at least one pixel of every opposite pair (k, k+8), so
+    //      a corner needs, for each of the pairs (0,8) (4,12) (2,10) (6,14), a brighter member (bright corner) or, for each,
+    //      a darker member (dark corner).  About one pixel in ten survives on textured frames.
+    const uint32_t t1 = (uint32_t)(t + 1) * 0x00010001u;
+    for (int idx = tid; idx < SH * NG; idx += 256) {
+        const int r = idx / NG, g = idx - r * NG;
+        const uint32_t* c = simg + (r + 3) * RWW + g;   // centre row of score row r
+        const uint32_t wc = c[0];
+        const uint32_t ce = __byte_perm(wc, 0, 0x4240), co = __byte_perm(wc, 0, 0x4341);
+        const uint32_t k1e = 0x80008000u - t1 - ce, k1o = 0x80008000u - t1 - co;   // + ring: bit 15 of a field = brighter
+        const uint32_t k2e = 0x80008000u - t1 + ce, k2o = 0x80008000u - t1 + co;   // - ring: bit 15 of a field = darker
+        PreAcc acc;
+        pre_pair(acc, c[3 * RWW], c[-3 * RWW], k1e, k1o, k2e, k2o, true);                                    // (0,+3) (0,-3)
+        uint32_t flag = ((acc.be | acc.de) | (acc.bo | acc.dout)) & 0x80008000u;
+        if (flag) {
+            pre_pair(acc, __funnelshift_r(c[0], c[1], 24), __funnelshift_r(c[-1], c[0], 8), k1e, k1o, k2e, k2o, false);   // (+3,0) (-3,0)
+            pre_pair(acc, __funnelshift_r(c[2 * RWW], c[2 * RWW + 1], 16), __funnelshift_r(c[-2 * RWW - 1], c[-2 * RWW], 16),
+                     k1e, k1o, k2e, k2o, false);                                                              // (+2,+2) (-2,-2)
+            pre_pair(acc, __funnelshift_r(c[-2 * RWW], c[-2 * RWW + 1], 16), __funnelshift_r(c[2 * RWW - 1], c[2 * RWW], 16),
+                     k1e, k1o, k2e, k2o, false);                                                              // (+2,-2) (-2,+2)
+            const uint32_t fe = (acc.be | acc.de) & 0x80008000u, fo = (acc.bo | acc.dout) & 0x80008000u;
+            // pixel i of the group: i = 0 -> fe bit 15, 1 -> fo bit 15, 2 -> fe bit 31, 3 -> fo bit 31
+            const uint32_t bits = ((fe >> 15) & 1u) | ((fo >> 14) & 2u) | ((fe >> 29) & 4u) | ((fo >> 28) & 8u);
+            const int gy = y0 - 1 + r;
+            if (bits && gy >= 3 && gy <= h - 4) {
 #pragma unroll
-                for (int k = 1; k < 16; ++k) {
-                    if ((k & 3) == 0) continue;
-                    const uint32_t f = classify(c[ring_off(k)], C);
-                    acc |= (f >> (15 - k)) & (0x00010001u << k);
+                for (int i = 0; i < 4; ++i) {
+                    const int sx = 4 * g + i - 3;
+                    const int gx = x0 - 1 + sx;
+                    if ((bits >> i & 1u) && sx >= 0 && sx < SW && gx >= 3 && gx <= w - 4)
+                        cand[atomicAdd(&ncand, 1)] = (uint16_t)(r * SW + sx);
                 }
-                const uint32_t inv = ~acc;   // low half: darker bits, high half: brighter bits
-                is_corner = run9(inv & 0xFFFFu) || run9(inv >> 16);
             }
         }
-        if (is_corner) cand[atomicAdd(&ncand, 1)] = (uint16_t)p;   // order irrelevant: scores are per pixel
     }
     __syncthreads();
 
-    // ---- pass 2: corner score for the survivors (dense over the candidate list)
-    const int nc = ncand;
-    for (int i = tid; i < nc; i += 256) {
+    // ---- pass 1: full segment test, dense over the candidate list (order irrelevant: scores are per pixel)
+    const uint32_t tt = (uint32_t)t;
+    const int nc0 = ncand;
+    for (int i = tid; i < nc0; i += 256) {
         const int p = cand[i];
+        const int sy = p / SW, sx = p - sy * SW;
+        const uint8_t* c = img + (sy + 3) * RW + sx + 3;
+        const uint32_t cv = c[0];
+        const uint32_t C = (0x8000u - (cv - tt)) + ((cv + tt + 0x8000u) << 16);
+        uint32_t acc = 0;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            const uint32_t f = classify(c[ring_off(k)], C);
+            acc |= k == 15 ? (f & (0x00010001u << 15)) : ((f >> (15 - k)) & (0x00010001u << k));
+        }
+        const uint32_t inv = ~acc;   // low half: darker bits, high half: brighter bits
+        if (run9(inv & 0xFFFFu) || run9(inv >> 16)) corner[atomicAdd(&ncorner, 1)] = (uint16_t)p;
+    }
+    __syncthreads();
+
+    // ---- pass 2: corner score for the survivors (dense over the corner list)
+    const int nc = ncorner;
+    for (int i = tid; i < nc; i += 256) {
+        const int p = corner[i];
         const int sy = p / SW, sx = p - sy * SW;
         best[sy * SWP + sx] = (uint8_t)corner_best(img + (sy + 3) * RW + sx + 3);   // 1..255 for a corner
     }
     __syncthreads();
 
-    // ---- pass 3: NMS + mask, then one ordered segment per (row, tile): warp w owns rows 2w and 2w+1
+    // ---- pass 3: NMS + mask, then one ordered segment per (row, tile): warp w owns rows w, w + 8, ...
     const int warp = tid >> 5, ln = tid & 31;
     const size_t seg_lane = (size_t)fb.rows_cap * fb.ntx_cap;
-#pragma unroll
-    for (int rr = 0; rr < 2; ++rr) {
-        const int r = warp * 2 + rr;
+    const uint32_t lt = (1u << ln) - 1u;
+    for (int r = warp; r < TH; r += 8) {
         const int gy = y0 + r;
         if (gy >= h) break;   // warp-uniform
-        uint32_t bal[2];
-        uint32_t bv[2];
+        const size_t seg = (size_t)lane_id * seg_lane + (size_t)gy * ntx + blockIdx.x;
+        uint16_t* out = fb.segkp + seg * TW;
+        int total = 0;
 #pragma unroll
-        for (int half = 0; half < 2; ++half) {
-            const int x = ln + 32 * half;
+        for (int q = 0; q < TW / 32; ++q) {
+            const int x = ln + 32 * q;
             const uint8_t* b = best + (r + 1) * SWP + x + 1;
             const int s = b[0];
             bool keep = s != 0;
@@ -181,18 +230,13 @@ __global__ void __launch_bounds__(256) fast_tile_kernel(const uint8_t* __restric
                        s > b[SWP] && s > b[SWP + 1];
             }
             if (keep && mask) keep = mask[(size_t)lane_id * mask_lane + (size_t)gy * mask_pitch + x0 + x] != 0;
-            bal[half] = __ballot_sync(0xffffffffu, keep);
-            bv[half] = keep ? (uint32_t)(x | (s << 8)) : 0xffffffffu;
+            const uint32_t bal = __ballot_sync(0xffffffffu, keep);
+            if (keep) out[total + __popc(bal & lt)] = (uint16_t)(x | (s << 8));
+            total += __popc(bal);
         }
-        const int n0 = __popc(bal[0]), n1 = __popc(bal[1]);
-        const size_t seg = (size_t)lane_id * seg_lane + (size_t)gy * ntx + blockIdx.x;
-        uint16_t* out = fb.segkp + seg * TW;
-        const uint32_t lt = (1u << ln) - 1u;
-        if (bv[0] != 0xffffffffu) out[__popc(bal[0] & lt)] = (uint16_t)bv[0];
-        if (bv[1] != 0xffffffffu) out[n0 + __popc(bal[1] & lt)] = (uint16_t)bv[1];
         if (ln == 0) {
-            fb.segcnt[seg] = (uint8_t)(n0 + n1);
-            if (n0 + n1) atomicAdd(fb.rowtotal + (size_t)lane_id * fb.rows_cap + gy, n0 + n1);
+            fb.segcnt[seg] = (uint8_t)total;
+            if (total) atomicAdd(fb.rowtotal + (size_t)lane_id * fb.rows_cap + gy, total);
         }
     }
 }

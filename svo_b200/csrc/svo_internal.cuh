@@ -45,14 +45,14 @@ void launch_ingest(cudaStream_t st, const uint8_t* raw, size_t raw_pitch, size_t
 void launch_pyrdown(cudaStream_t st, uint8_t* pyr, const PyrGeom& g, int level, int batch, long long* launches);
 
 // ------------------------------------------------------------------------------------------------ fast.cu
-constexpr int kFastTW = 64;   // tile width: one (row, tile) segment holds at most 64 keypoints
-constexpr int kFastTH = 16;
+constexpr int kFastTW = 128;  // tile width: one (row, tile) segment holds at most 128 keypoints
+constexpr int kFastTH = 32;
 
 struct FastBufs {
     // per lane strides are in elements of the respective type
     int* rowtotal;        // [B][rows_cap]           keypoints per image row (atomic counters, zeroed per call)
     uint8_t* segcnt;      // [B][rows_cap * ntx_cap] keypoints per (row, tile) segment
-    uint16_t* segkp;      // [B][rows_cap * ntx_cap * 64] x_local | best << 8, in x order inside a segment
+    uint16_t* segkp;      // [B][rows_cap * ntx_cap * kFastTW] x_local | best << 8, in x order inside a segment
     int rows_cap, ntx_cap;
     float2* kp_xy;        // [B][kp_cap]
     float* kp_resp;       // [B][kp_cap]
