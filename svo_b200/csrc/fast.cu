@@ -14,6 +14,8 @@
 //                      a per-(row, tile) segment of kept keypoints written in x order via warp ballots.
 //   fast_gather_kernel one CTA per image row: offset = keypoints in all earlier rows (sum of the per-row counters) +
 //                      segments to the left; copies the segments to the final (x, y, response) list.
+#include <type_traits>
+
 #include "svo_internal.cuh"
 
 namespace svo {
@@ -23,102 +25,79 @@ namespace {
 constexpr int TW = kFastTW, TH = kFastTH;
 constexpr int RW = TW + 8, RH = TH + 8;   // staged image region (halo 3 for the ring + 1 for the NMS neighbours), origin (x0-4, y0-4)
 constexpr int RWW = RW / 4;               // words per staged row
-constexpr int SW = TW + 2, SH = TH + 2;   // score region, origin (x0-1, y0-1) = staged (3, 3)
-constexpr int SWP = SW + 2;               // padded score row
+constexpr int SH = TH + 2;   // score region, origin (x0-1, y0-1) = staged (3, 3)
 constexpr int NG = RWW;                   // 4-pixel groups per score row (staged columns 4g .. 4g+3)
 
-// ring offsets in the staged tile (row pitch RW), order of OpenCV's pixel[] table
-__device__ __forceinline__ constexpr int ring_off(int k)
+// ---- packed arithmetic: two pixels per 32-bit register (16-bit fields); a 4-pixel group = an "even" register (pixels
+// 0, 2) and an "odd" one (pixels 1, 3).  sm_100a has 3-input packed min/max (VIMNMX3.U16x2), which ptxas forms from
+// nested min.u16x2 / max.u16x2.
+__device__ __forceinline__ uint32_t pmin(uint32_t a, uint32_t b)
 {
-    constexpr int dx[16] = {0, 1, 2, 3, 3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1};
-    constexpr int dy[16] = {3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1, 0, 1, 2, 3};
-    return dy[k] * RW + dx[k];
+    uint32_t d;
+    asm("min.u16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+    return d;
+}
+__device__ __forceinline__ uint32_t pmax(uint32_t a, uint32_t b)
+{
+    uint32_t d;
+    asm("max.u16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+    return d;
+}
+__device__ __forceinline__ uint32_t pmin3(uint32_t a, uint32_t b, uint32_t c) { return pmin(pmin(a, b), c); }
+__device__ __forceinline__ uint32_t pmax3(uint32_t a, uint32_t b, uint32_t c) { return pmax(pmax(a, b), c); }
+__device__ __forceinline__ uint32_t even_px(uint32_t w) { return __byte_perm(w, 0, 0x4240); }   // bytes 0, 2 -> fields
+__device__ __forceinline__ uint32_t odd_px(uint32_t w) { return __byte_perm(w, 0, 0x4341); }    // bytes 1, 3 -> fields
+
+// the staged word holding bytes (4g + dx .. 4g + dx + 3) of the row at c (c points at word g)
+template <int DX>
+__device__ __forceinline__ uint32_t ring_word(const uint32_t* __restrict__ c)
+{
+    if constexpr (DX == 0) return c[0];
+    else if constexpr (DX > 0) return __funnelshift_r(c[0], c[1], 8 * DX);
+    else return __funnelshift_r(c[-1], c[0], 32 + 8 * DX);
 }
 
-// One multiply classifies a ring pixel v against both thresholds: with C = (0x8000 - lo) | ((hi + 0x8000) << 16),
-// C + v * 0xFFFF0001 has bit 15 = (v >= lo) = "not darker" and bit 31 = (v <= hi) = "not brighter" (no carry between halves).
-__device__ __forceinline__ uint32_t classify(uint32_t v, uint32_t C) { return C + v * 0xFFFF0001u; }
-
-// true iff the 16-bit circular mask m has 9 contiguous set bits
-__device__ __forceinline__ bool run9(uint32_t m)
+// cornerScore<16> for two pixels at once.  D[k] = centre + 256 - ring_k (1..511 per field).  With d = D - 256:
+//   best = max over the 16 arcs of 9 of max(min d, min -d) = max(max_arcs min9 D, 512 - min_arcs max9 D) - 256.
+// Returns best + 256 per field.
+__device__ __forceinline__ uint32_t packed_best(const uint32_t (&D)[16])
 {
-    uint32_t dd = m | (m << 16);
-    uint32_t a = dd & (dd >> 1);
-    uint32_t b = a & (a >> 2);
-    uint32_t c = b & (b >> 4);
-    uint32_t d = c & (dd >> 8);
-    return (d & 0xFFFFu) != 0;
-}
-
-__device__ __forceinline__ int min3(int a, int b, int c) { return min(min(a, b), c); }
-__device__ __forceinline__ int max3(int a, int b, int c) { return max(max(a, b), c); }
-
-// ---- packed pre-test: four horizontally adjacent pixels per thread, two per 32-bit register (16-bit fields).
-// For a field holding ring value r and centre c:  (0x8000 - (c+t+1)) + r has bit 15 set iff r > c + t  (brighter),
-//                                                  (0x8000 + c-t-1) - r has bit 15 set iff r < c - t  (darker);
-// every field stays inside [0x7DFF, 0x80FE], so no carry or borrow crosses the fields.
-struct PreAcc {
-    uint32_t be, bo, de, dout;   // running AND over opposite pairs of (flag_k | flag_k+8): bright/dark x even/odd pixels
-};
-
-__device__ __forceinline__ void pre_pair(PreAcc& acc, uint32_t wa, uint32_t wb, uint32_t k1e, uint32_t k1o, uint32_t k2e,
-                                         uint32_t k2o, bool first)
-{
-    const uint32_t ae = __byte_perm(wa, 0, 0x4240), ao = __byte_perm(wa, 0, 0x4341);   // bytes (0,2) / (1,3) as 16-bit fields
-    const uint32_t be = __byte_perm(wb, 0, 0x4240), bo = __byte_perm(wb, 0, 0x4341);
-    const uint32_t bre = (ae + k1e) | (be + k1e), bro = (ao + k1o) | (bo + k1o);
-    const uint32_t dke = (k2e - ae) | (k2e - be), dko = (k2o - ao) | (k2o - bo);
-    if (first) { acc.be = bre; acc.bo = bro; acc.de = dke; acc.dout = dko; }
-    else { acc.be &= bre; acc.bo &= bro; acc.de &= dke; acc.dout &= dko; }
-}
-
-// cornerScore<16>: best = max over arcs of min(d) and min(-d).
-// Both polarities are computed as minima (of d and of e = -d).  Writing the bright side as -max(d) made nvcc 12.9 emit
-// VIMNMX3 with the negation dropped for sm_100a (wrong scores on the B200; caught by the parity tests) -- keep it this way.
-__device__ __forceinline__ int corner_best(const uint8_t* __restrict__ p)
-{
-    const int c = p[0];
-    int d[16], e[16];
+    uint32_t mn3[16], mx3[16];
 #pragma unroll
     for (int k = 0; k < 16; ++k) {
-        const int v = p[ring_off(k)];
-        d[k] = c - v;
-        e[k] = v - c;
+        mn3[k] = pmin3(D[k], D[(k + 1) & 15], D[(k + 2) & 15]);
+        mx3[k] = pmax3(D[k], D[(k + 1) & 15], D[(k + 2) & 15]);
     }
-    int d3[16], e3[16];
+    uint32_t hi = 0u, lo = 0xffffffffu;
 #pragma unroll
-    for (int k = 0; k < 16; ++k) {
-        d3[k] = min3(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
-        e3[k] = min3(e[k], e[(k + 1) & 15], e[(k + 2) & 15]);
+    for (int k = 0; k < 16; k += 2) {
+        const uint32_t a = pmin3(mn3[k], mn3[(k + 3) & 15], mn3[(k + 6) & 15]);
+        const uint32_t b = pmin3(mn3[k + 1], mn3[(k + 4) & 15], mn3[(k + 7) & 15]);
+        hi = pmax3(hi, a, b);
+        const uint32_t c = pmax3(mx3[k], mx3[(k + 3) & 15], mx3[(k + 6) & 15]);
+        const uint32_t d = pmax3(mx3[k + 1], mx3[(k + 4) & 15], mx3[(k + 7) & 15]);
+        lo = pmin3(lo, c, d);
     }
-    int best = -256;
-#pragma unroll
-    for (int k = 0; k < 16; ++k) {
-        const int d9 = min3(d3[k], d3[(k + 3) & 15], d3[(k + 6) & 15]);
-        const int e9 = min3(e3[k], e3[(k + 3) & 15], e3[(k + 6) & 15]);
-        best = max3(best, d9, e9);
-    }
-    return best;
+    return pmax(hi, 0x02000200u - lo);
 }
+
+// scalar cornerScore<16> kept for reference in comments of the tests: see oracle/svo_oracle.c:orc_corner_score
 
 __global__ void __launch_bounds__(256) fast_tile_kernel(const uint8_t* __restrict__ raw, size_t raw_pitch, size_t raw_lane,
                                                         int w, int h, int t, int nms, const uint8_t* __restrict__ mask,
                                                         size_t mask_pitch, size_t mask_lane, FastBufs fb, int ntx)
 {
-    __shared__ __align__(16) uint32_t simg_pad[RH * RWW + 2];   // one pad word on each side: the pre-test reads words g-1, g+1
-    __shared__ uint8_t best[SH * SWP];
-    __shared__ uint16_t cand[SH * SW];     // pixels that pass the packed pre-test
-    __shared__ uint16_t corner[SH * SW];   // pixels that pass the full segment test
-    __shared__ int ncand, ncorner;
-
+    __shared__ __align__(16) uint32_t simg_pad[RH * RWW + 2];   // one pad word on each side: ring_word reads words g-1, g+1
+    __shared__ __align__(16) uint32_t sbest_pad[SH * RWW + 2];  // excess of the score over the threshold, one byte per pixel,
+                                                                // same column layout as the staged image (0 = no corner)
     uint32_t* simg = simg_pad + 1;
-    const uint8_t* img = reinterpret_cast<const uint8_t*>(simg);
+    uint32_t* sbest = sbest_pad + 1;
     const int tid = threadIdx.x;
     const int x0 = blockIdx.x * TW, y0 = blockIdx.y * TH;
     const int lane_id = blockIdx.z;
     const uint8_t* src = raw + (size_t)lane_id * raw_lane;
 
-    if (tid == 0) { ncand = 0; ncorner = 0; simg_pad[0] = 0; simg_pad[RH * RWW + 1] = 0; }
+    if (tid == 0) { simg_pad[0] = 0; simg_pad[RH * RWW + 1] = 0; sbest_pad[0] = 0; sbest_pad[SH * RWW + 1] = 0; }
 
     // ---- stage the (TW+8) x (TH+8) region; coordinates are clamped to the image (clamped pixels are never used by a
     //      valid candidate: those sit at least 3 px inside the image)
@@ -138,101 +117,104 @@ __global__ void __launch_bounds__(256) fast_tile_kernel(const uint8_t* __restric
         }
         simg[i] = v;
     }
-    for (int i = tid; i < SH * SWP; i += 256) best[i] = 0;
     __syncthreads();
 
-    // ---- pass 0: packed pre-test on 4-pixel groups.  A 9-arc holds at least one pixel of every opposite pair (k, k+8), so
-    //      a corner needs, for each of the pairs (0,8) (4,12) (2,10) (6,14), a brighter member (bright corner) or, for each,
-    //      a darker member (dark corner).  About one pixel in ten survives on textured frames.
-    const uint32_t t1 = (uint32_t)(t + 1) * 0x00010001u;
+    // ---- pass 1: dense packed corner score of every 4-pixel group of the score region (rows y0-1 .. y0+TH, staged
+    //      columns 0 .. RW-1): sbest byte = max(best - t, 0), where best = cornerScore + 1.
+    const uint32_t bias = 0x01000100u;
+    const uint32_t tt = (uint32_t)t * 0x00010001u;
     for (int idx = tid; idx < SH * NG; idx += 256) {
         const int r = idx / NG, g = idx - r * NG;
         const uint32_t* c = simg + (r + 3) * RWW + g;   // centre row of score row r
         const uint32_t wc = c[0];
-        const uint32_t ce = __byte_perm(wc, 0, 0x4240), co = __byte_perm(wc, 0, 0x4341);
-        const uint32_t k1e = 0x80008000u - t1 - ce, k1o = 0x80008000u - t1 - co;   // + ring: bit 15 of a field = brighter
-        const uint32_t k2e = 0x80008000u - t1 + ce, k2o = 0x80008000u - t1 + co;   // - ring: bit 15 of a field = darker
-        PreAcc acc;
-        pre_pair(acc, c[3 * RWW], c[-3 * RWW], k1e, k1o, k2e, k2o, true);                                    // (0,+3) (0,-3)
-        uint32_t flag = ((acc.be | acc.de) | (acc.bo | acc.dout)) & 0x80008000u;
-        if (flag) {
-            pre_pair(acc, __funnelshift_r(c[0], c[1], 24), __funnelshift_r(c[-1], c[0], 8), k1e, k1o, k2e, k2o, false);   // (+3,0) (-3,0)
-            pre_pair(acc, __funnelshift_r(c[2 * RWW], c[2 * RWW + 1], 16), __funnelshift_r(c[-2 * RWW - 1], c[-2 * RWW], 16),
-                     k1e, k1o, k2e, k2o, false);                                                              // (+2,+2) (-2,-2)
-            pre_pair(acc, __funnelshift_r(c[-2 * RWW], c[-2 * RWW + 1], 16), __funnelshift_r(c[2 * RWW - 1], c[2 * RWW], 16),
-                     k1e, k1o, k2e, k2o, false);                                                              // (+2,-2) (-2,+2)
-            const uint32_t fe = (acc.be | acc.de) & 0x80008000u, fo = (acc.bo | acc.dout) & 0x80008000u;
-            // pixel i of the group: i = 0 -> fe bit 15, 1 -> fo bit 15, 2 -> fe bit 31, 3 -> fo bit 31
-            const uint32_t bits = ((fe >> 15) & 1u) | ((fo >> 14) & 2u) | ((fe >> 29) & 4u) | ((fo >> 28) & 8u);
-            const int gy = y0 - 1 + r;
-            if (bits && gy >= 3 && gy <= h - 4) {
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const int sx = 4 * g + i - 3;
-                    const int gx = x0 - 1 + sx;
-                    if ((bits >> i & 1u) && sx >= 0 && sx < SW && gx >= 3 && gx <= w - 4)
-                        cand[atomicAdd(&ncand, 1)] = (uint16_t)(r * SW + sx);
-                }
+        const uint32_t be = even_px(wc) + bias, bo = odd_px(wc) + bias;   // D = b - ring
+        uint32_t De[16], Do[16];
+        auto ring = [&](auto kk, auto dxx, auto dyy) {
+            constexpr int K = decltype(kk)::value, DX = decltype(dxx)::value, DY = decltype(dyy)::value;
+            const uint32_t v = ring_word<DX>(c + DY * RWW);
+            De[K] = be - even_px(v);
+            Do[K] = bo - odd_px(v);
+        };
+#define RING(K, DX, DY) ring(std::integral_constant<int, K>{}, std::integral_constant<int, DX>{}, std::integral_constant<int, DY>{})
+        // the compass points first: a 9-arc holds a pixel of every opposite pair, so a corner needs a darker member in both
+        // (0,8) and (4,12), or a brighter member in both.  darker: ring < c - t <=> D >= 257 + t; brighter: D <= 255 - t.
+        RING(0, 0, 3); RING(8, 0, -3); RING(4, 3, 0); RING(12, -3, 0);
+        {
+            const uint32_t kd = 0x7eff7effu - tt;   // D + kd: bit 15 of a field set <=> D >= 257 + t
+            const uint32_t kb = 0x80ff80ffu - tt;   // kb - D: bit 15 of a field set <=> D <= 255 - t
+            const uint32_t fe = (((De[0] + kd) | (De[8] + kd)) & ((De[4] + kd) | (De[12] + kd))) |
+                                (((kb - De[0]) | (kb - De[8])) & ((kb - De[4]) | (kb - De[12])));
+            const uint32_t fo = (((Do[0] + kd) | (Do[8] + kd)) & ((Do[4] + kd) | (Do[12] + kd))) |
+                                (((kb - Do[0]) | (kb - Do[8])) & ((kb - Do[4]) | (kb - Do[12])));
+            if (((fe | fo) & 0x80008000u) == 0) {   // no pixel of the group can be a corner
+                sbest[r * RWW + g] = 0;
+                continue;
             }
         }
-    }
-    __syncthreads();
-
-    // ---- pass 1: full segment test, dense over the candidate list (order irrelevant: scores are per pixel)
-    const uint32_t tt = (uint32_t)t;
-    const int nc0 = ncand;
-    for (int i = tid; i < nc0; i += 256) {
-        const int p = cand[i];
-        const int sy = p / SW, sx = p - sy * SW;
-        const uint8_t* c = img + (sy + 3) * RW + sx + 3;
-        const uint32_t cv = c[0];
-        const uint32_t C = (0x8000u - (cv - tt)) + ((cv + tt + 0x8000u) << 16);
-        uint32_t acc = 0;
+        RING(1, 1, 3); RING(2, 2, 2); RING(3, 3, 1); RING(5, 3, -1); RING(6, 2, -2); RING(7, 1, -3);
+        RING(9, -1, -3); RING(10, -2, -2); RING(11, -3, -1); RING(13, -3, 1); RING(14, -2, 2); RING(15, -1, 3);
+#undef RING
+        const uint32_t floor_ = 0x01000100u + tt;                     // best + 256 <= 256 + t  ->  not a corner
+        const uint32_t se = pmax(packed_best(De), floor_) - floor_;   // best - t, 0 if not a corner
+        const uint32_t so = pmax(packed_best(Do), floor_) - floor_;
+        uint32_t out = __byte_perm(se, so, 0x6240);                   // bytes: pixel 0, 1, 2, 3
+        // pixels outside the 3-px frame of the image are not candidates
+        const int gy = y0 - 1 + r, gx = x0 - 4 + 4 * g;
+        if (gy < 3 || gy > h - 4) out = 0;
+        else if (gx < 3 || gx + 3 > w - 4) {
 #pragma unroll
-        for (int k = 0; k < 16; ++k) {
-            const uint32_t f = classify(c[ring_off(k)], C);
-            acc |= k == 15 ? (f & (0x00010001u << 15)) : ((f >> (15 - k)) & (0x00010001u << k));
+            for (int i = 0; i < 4; ++i)
+                if (gx + i < 3 || gx + i > w - 4) out &= ~(0xffu << (8 * i));
         }
-        const uint32_t inv = ~acc;   // low half: darker bits, high half: brighter bits
-        if (run9(inv & 0xFFFFu) || run9(inv >> 16)) corner[atomicAdd(&ncorner, 1)] = (uint16_t)p;
+        sbest[r * RWW + g] = out;
     }
     __syncthreads();
 
-    // ---- pass 2: corner score for the survivors (dense over the corner list)
-    const int nc = ncorner;
-    for (int i = tid; i < nc; i += 256) {
-        const int p = corner[i];
-        const int sy = p / SW, sx = p - sy * SW;
-        best[sy * SWP + sx] = (uint8_t)corner_best(img + (sy + 3) * RW + sx + 3);   // 1..255 for a corner
-    }
-    __syncthreads();
-
-    // ---- pass 3: NMS + mask, then one ordered segment per (row, tile): warp w owns rows w, w + 8, ...
+    // ---- pass 2: strict 3x3 NMS + mask, then one ordered segment per (row, tile): a warp owns a row, a lane a 4-pixel group
     const int warp = tid >> 5, ln = tid & 31;
     const size_t seg_lane = (size_t)fb.rows_cap * fb.ntx_cap;
     const uint32_t lt = (1u << ln) - 1u;
+    // OpenCV compares scores (= best - 1); a corner of score 0 (threshold 0 only) never beats a non-corner's 0
+    const uint32_t nms_floor = (nms && t == 0) ? 0x00010001u : 0u;
     for (int r = warp; r < TH; r += 8) {
         const int gy = y0 + r;
         if (gy >= h) break;   // warp-uniform
-        const size_t seg = (size_t)lane_id * seg_lane + (size_t)gy * ntx + blockIdx.x;
-        uint16_t* out = fb.segkp + seg * TW;
-        int total = 0;
+        const uint32_t* b = sbest + (r + 1) * RWW + ln + 1;   // tile pixel x = 4 ln + i sits in staged group ln + 1
+        const uint32_t wc = b[0];
+        uint32_t bits = 0;
+        if (wc) {
+            uint32_t me = nms_floor, mo = nms_floor;
+            if (nms) {
 #pragma unroll
-        for (int q = 0; q < TW / 32; ++q) {
-            const int x = ln + 32 * q;
-            const uint8_t* b = best + (r + 1) * SWP + x + 1;
-            const int s = b[0];
-            bool keep = s != 0;
-            if (keep && nms) {
-                // stored value = best = score + 1 (0 = no corner); OpenCV compares scores, and a corner of score 0
-                // (only possible at threshold 0) never beats a non-corner neighbour's 0: hence s > 1
-                keep = s > 1 && s > b[-1] && s > b[1] && s > b[-SWP - 1] && s > b[-SWP] && s > b[-SWP + 1] && s > b[SWP - 1] &&
-                       s > b[SWP] && s > b[SWP + 1];
+                for (int dr = -1; dr <= 1; ++dr) {
+                    const uint32_t* q = b + dr * RWW;
+                    const uint32_t L = __funnelshift_r(q[-1], q[0], 24), R = __funnelshift_r(q[0], q[1], 8);
+                    if (dr == 0) { me = pmax3(me, even_px(L), even_px(R)); mo = pmax3(mo, odd_px(L), odd_px(R)); }
+                    else {
+                        me = pmax(me, pmax3(even_px(L), even_px(q[0]), even_px(R)));
+                        mo = pmax(mo, pmax3(odd_px(L), odd_px(q[0]), odd_px(R)));
+                    }
+                }
             }
-            if (keep && mask) keep = mask[(size_t)lane_id * mask_lane + (size_t)gy * mask_pitch + x0 + x] != 0;
-            const uint32_t bal = __ballot_sync(0xffffffffu, keep);
-            if (keep) out[total + __popc(bal & lt)] = (uint16_t)(x | (s << 8));
-            total += __popc(bal);
+            // keep <=> s > m <=> (s + 0x7fff) - m has bit 15 set (fields stay inside [0x7f00, 0x80fe])
+            const uint32_t ke = (even_px(wc) + 0x7fff7fffu) - me, ko = (odd_px(wc) + 0x7fff7fffu) - mo;
+            bits = ((ke >> 15) & 1u) | ((ko >> 14) & 2u) | ((ke >> 29) & 4u) | ((ko >> 28) & 8u);
+            if (bits && mask) {
+                const uint8_t* mrow = mask + (size_t)lane_id * mask_lane + (size_t)gy * mask_pitch + x0 + 4 * ln;
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    if ((bits >> i & 1u) && mrow[i] == 0) bits &= ~(1u << i);
+            }
+        }
+        const uint32_t b0 = __ballot_sync(0xffffffffu, bits & 1u), b1 = __ballot_sync(0xffffffffu, bits & 2u);
+        const uint32_t b2 = __ballot_sync(0xffffffffu, bits & 4u), b3 = __ballot_sync(0xffffffffu, bits & 8u);
+        const int total = __popc(b0) + __popc(b1) + __popc(b2) + __popc(b3);
+        const size_t seg = (size_t)lane_id * seg_lane + (size_t)gy * ntx + blockIdx.x;
+        if (bits) {
+            uint16_t* out = fb.segkp + seg * TW + __popc(b0 & lt) + __popc(b1 & lt) + __popc(b2 & lt) + __popc(b3 & lt);
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                if (bits >> i & 1u) *out++ = (uint16_t)((4 * ln + i) | (((wc >> (8 * i)) & 0xffu) << 8));
         }
         if (ln == 0) {
             fb.segcnt[seg] = (uint8_t)total;
@@ -242,7 +224,7 @@ __global__ void __launch_bounds__(256) fast_tile_kernel(const uint8_t* __restric
 }
 
 // grid = (h, batch), 128 threads
-__global__ void __launch_bounds__(128) fast_gather_kernel(int w, int h, int nms, FastBufs fb, int ntx)
+__global__ void __launch_bounds__(128) fast_gather_kernel(int w, int h, int t, int nms, FastBufs fb, int ntx)
 {
     __shared__ int red[4];
     __shared__ int segoff[1024];
@@ -288,7 +270,7 @@ __global__ void __launch_bounds__(128) fast_gather_kernel(int w, int h, int nms,
             const int idx = base + segoff[s] + j;
             if (idx < fb.kp_cap) {
                 oxy[idx] = make_float2((float)(s * TW + (int)(e & 255u)), (float)y);
-                orp[idx] = nms ? (float)((int)(e >> 8) - 1) : 0.f;
+                orp[idx] = nms ? (float)((int)(e >> 8) + t - 1) : 0.f;   // stored byte = best - t, score = best - 1
             }
         }
     }
@@ -329,7 +311,7 @@ void launch_fast(cudaStream_t st, const uint8_t* raw, size_t raw_pitch, size_t r
     dim3 grid(ntx, (h + TH - 1) / TH, batch);
     fast_tile_kernel<<<grid, 256, 0, st>>>(raw, raw_pitch, raw_lane, w, h, threshold, nms, mask, mask_pitch, mask_lane,
                                            fb, ntx);
-    fast_gather_kernel<<<dim3(h, batch), 128, 0, st>>>(w, h, nms, fb, ntx);
+    fast_gather_kernel<<<dim3(h, batch), 128, 0, st>>>(w, h, threshold, nms, fb, ntx);
     if (launches) *launches += 2;
 }
 
