@@ -34,8 +34,8 @@ RING = 8   # frames per stream kept resident; time stamps 0,1,2,3,4,3,2,1 so tha
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=40)
-    ap.add_argument("--warmup", type=int, default=8)
+    ap.add_argument("--steps", type=int, default=300)
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--streams", type=int, default=64, help="independent sequences per GPU")
     ap.add_argument("--workload", default="C1", choices=sorted(synth.WORKLOADS), help="per-stream shape")
@@ -75,7 +75,7 @@ def pyramid_pixels(w, h, levels):
 
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+    Q = ("timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
@@ -83,12 +83,14 @@ class ClockSampler:
         self.p = None
         try:
             self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
-                                       "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                       "--format=csv,noheader,nounits", "-lms", "50"], stdout=self.f,
                                       stderr=subprocess.DEVNULL)
         except Exception:
             self.p = None
 
-    def stop(self):
+    def stop(self, t0=None, t1=None):
+        """Summary of the samples taken between host times t0 and t1 (time.time()); all samples if none fall inside."""
+        import datetime
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
         if self.p is None:
             return out
@@ -99,22 +101,28 @@ class ClockSampler:
             self.p.kill()
         self.f.flush()
         self.f.seek(0)
-        sm, mx, reasons = [], [], set()
+        rows = []
         for line in self.f.read().splitlines():
             c = [x.strip() for x in line.split(",")]
             if len(c) < 9:
                 continue
             try:
-                sm.append(float(c[1]))
-                mx.append(float(c[2]))
+                ts = datetime.datetime.strptime(c[0], "%Y/%m/%d %H:%M:%S.%f").timestamp()
+                rows.append((ts, float(c[1]), float(c[2]), float(c[3]), c[5:9]))
             except ValueError:
                 continue
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), c[5:9]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
         os.unlink(self.f.name)
-        if sm:
-            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), reasons=sorted(reasons), samples=len(sm))
+        inside = [r for r in rows if t0 is not None and t0 <= r[0] <= t1]
+        use = inside or rows
+        if use:
+            reasons = set()
+            for r in use:
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[4]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            out.update(sm_mhz=float(np.median([r[1] for r in use])), sm_max_mhz=float(max(r[2] for r in use)),
+                       power_w=float(np.median([r[3] for r in use])), reasons=sorted(reasons), samples=len(use),
+                       window="timed region" if inside else "whole run (no sample fell inside the timed region)")
         return out
 
 
@@ -235,29 +243,38 @@ def run_b200(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    # ---- end to end: host frames in, results out, every step (also yields the keypoint statistics)
+    # ---- end to end: host frames in, results out, every step.  svo_gpu_step_pipelined copies step i+1's frames (pinned host
+    #      memory) on a second stream while step i computes; every step still waits for its own results on the host.
+    def hptr(i):
+        return host[i % RING].data_ptr()
+
     fe.reset()
     for i in range(W):
-        fe.step_host_ptr(host[i % RING].data_ptr(), w, w * h)
+        fe.step_host_pipelined(hptr(i), hptr(i + 1), w, w * h)
     barrier()
     ev[0].record(stream)
-    kp_sum = bk_sum = trk_sum = ok_sum = 0
     for i in range(W, W + K):
-        fe.step_host_ptr(host[i % RING].data_ptr(), w, w * h)
-        kp_sum += int(fe.n_keypoints.sum()); bk_sum += int(fe.n_bucketed.sum()); trk_sum += int(fe.n_tracked.sum())
-        ok_sum += int(sum(int(fe.status[b, :fe.n_tracked[b]].sum()) for b in range(S)))
+        fe.step_host_pipelined(hptr(i), hptr(i + 1), w, w * h)
     ev[1].record(stream)
     barrier()
     e2e_ms = max_over_ranks(ev[0].elapsed_time(ev[1]))
+    # statistics of the workload (outside any timed region)
+    kp_sum = bk_sum = trk_sum = ok_sum = 0
+    NS = 8
+    for i in range(W + K, W + K + NS):
+        fe.step_host_pipelined(hptr(i), hptr(i + 1), w, w * h)
+        kp_sum += int(fe.n_keypoints.sum()); bk_sum += int(fe.n_bucketed.sum()); trk_sum += int(fe.n_tracked.sum())
+        ok_sum += int(sum(int(fe.status[b, :fe.n_tracked[b]].sum()) for b in range(S)))
 
     # ---- device resident: frames already in HBM, nothing returned to the host
+    sampler = ClockSampler(local) if rank == 0 else None   # nvidia-smi needs a moment to start: launched before the warm-up
     fe.reset()
     for i in range(W):
         fe.step_device(dev[i % RING].data_ptr(), pitch, h * pitch)
     ctx.step_profile(True)
     launches0 = ctx.launch_count
     barrier()
-    sampler = ClockSampler(local) if rank == 0 else None
+    t_start = time.time()
     ev[2].record(stream)
     stage = np.zeros(4)
     iters = 0
@@ -267,7 +284,7 @@ def run_b200(args):
         iters += ctx.last_klt_iterations
     ev[3].record(stream)
     barrier()
-    clocks = sampler.stop() if sampler else None
+    clocks = sampler.stop(t_start, time.time()) if sampler else None
     dev_ms = max_over_ranks(ev[2].elapsed_time(ev[3]))
     launches = ctx.launch_count - launches0
     ctx.step_profile(False)
@@ -278,8 +295,9 @@ def run_b200(args):
 
     frames_total = world * S * K
     stage_ms = stage / K                                      # ingest+pyramid, LK, FAST, bucketing (per step, this rank)
-    kp = kp_sum / (S * K)
-    n_trk = trk_sum / (S * K)
+    kp = kp_sum / (S * NS)
+    n_trk = trk_sum / (S * NS)
+    bk = bk_sum / (S * NS)
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -292,7 +310,7 @@ def run_b200(args):
         "pyramid": S * npyr,                                  # read level 0 once + write levels >= 1
         "klt": S * (2 * npyr + 29 * n_trk),                   # both pyramids once + per-track in/out
         "fast": S * (w * h + 12 * kp),
-        "bucket": S * 12 * (kp + bk_sum / (S * K)),
+        "bucket": S * 12 * (kp + bk),
     }
     names = ["pyramid", "klt", "fast", "bucket"]
     kernels = {n: {"ms": float(stage_ms[i]), "alg_bytes": float(alg[n]),
@@ -304,7 +322,7 @@ def run_b200(args):
     except Exception:
         pass
     klt = kernels["klt"]
-    it_per_track = iters / max(trk_sum, 1)
+    it_per_track = iters / max(S * n_trk * K, 1)
     # op model of SURVEY 8d: 18 lane-ops per setup pixel per level, 8 per iteration pixel
     lane_ops = (levels * wl["win"] ** 2 * 18 + it_per_track * wl["win"] ** 2 * 8) * n_trk * S
     sm_mhz = (clocks or {}).get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)
@@ -313,7 +331,6 @@ def run_b200(args):
         "value": frames_total / (dev_ms * 1e-3), "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u8/int32 + f32 epilogue", "data": "synthetic", "config": workload_config(args, wl),
-        "klt_tracks_per_s": world * trk_sum / K * K / (dev_ms * 1e-3) / K if K else None,
         "e2e": {"value": frames_total / (e2e_ms * 1e-3), "unit": "frames/s", "h2d_bytes_per_step": S * w * h,
                 "d2h_bytes_per_step": fe.d2h_bytes, "ms_per_step": e2e_ms / K},
         "gpu_launches": int(launches),
@@ -327,10 +344,10 @@ def run_b200(args):
                             "peak_lane_ops_per_s": 148 * 128 * sm_mhz * 1e6,
                             "frac": (lane_ops / (klt["ms"] * 1e-3)) / (148 * 128 * sm_mhz * 1e6) if klt["ms"] > 0 else None},
         "kernels": kernels,
-        "stats": {"keypoints_per_frame": kp, "bucketed_per_frame": bk_sum / (S * K), "tracks_per_frame": n_trk,
+        "stats": {"keypoints_per_frame": kp, "bucketed_per_frame": bk, "tracks_per_frame": n_trk,
                   "status_ok_frac": ok_sum / max(trk_sum, 1)},
     }
-    line["klt_tracks_per_s"] = world * trk_sum / K * K / (dev_ms * 1e-3)
+    line["klt_tracks_per_s"] = world * S * n_trk * K / (dev_ms * 1e-3)
     if world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
         ns = min(S, threads)

@@ -177,6 +177,14 @@ typedef struct svo_gpu_step_outputs {
 SVO_GPU_API int svo_gpu_step(svo_gpu_ctx* ctx, const uint8_t* images, int mem_kind, size_t stride_bytes,
                              size_t image_stride_bytes, int batch, const svo_gpu_step_params* params,
                              const svo_gpu_step_outputs* outputs_or_null);
+/* The same step with the frame ingest pipelined (the reference's AsyncImageLoader,
+ * include/async_image_loader.h:27-47, has the next frames decoded before they are needed): `next_images` (host memory,
+ * same geometry, or NULL) are the frames of the FOLLOWING call; their host-to-device copy is started now on a second
+ * stream and overlaps this step's kernels.  The following call must pass that same pointer as `images` (otherwise the
+ * prefetch is discarded and the frames are copied normally).  The caller keeps `next_images` unchanged until then. */
+SVO_GPU_API int svo_gpu_step_pipelined(svo_gpu_ctx* ctx, const uint8_t* images, const uint8_t* next_images, int mem_kind,
+                                       size_t stride_bytes, size_t image_stride_bytes, int batch,
+                                       const svo_gpu_step_params* params, const svo_gpu_step_outputs* outputs_or_null);
 /* Forgets the previous frame and tracks of every lane (start of a new set of sequences). */
 SVO_GPU_API int svo_gpu_step_reset(svo_gpu_ctx* ctx);
 /* Number of kernel launches (graph kernel nodes included) issued by this context so far. */

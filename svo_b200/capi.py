@@ -45,6 +45,8 @@ SYMBOLS = {
     "svo_gpu_last_klt_iterations": (C.c_longlong, [C.c_void_p]),
     "svo_gpu_step": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_size_t, C.c_size_t, C.c_int, C.c_void_p,
                                C.c_void_p]),
+    "svo_gpu_step_pipelined": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_size_t, C.c_size_t, C.c_int,
+                                         C.c_void_p, C.c_void_p]),
     "svo_gpu_step_reset": (C.c_int, [C.c_void_p]),
     "svo_gpu_launch_count": (C.c_longlong, [C.c_void_p]),
     "svo_gpu_step_profile": (C.c_int, [C.c_void_p, C.c_int, _f32p]),
@@ -228,6 +230,12 @@ class Context:
     def step(self, images_ptr, mem_kind, stride, image_stride, batch, params, outputs=None):
         self._ck(self.lib.svo_gpu_step(self.h, C.c_void_p(images_ptr), mem_kind, stride, image_stride, batch,
                                        C.byref(params), C.byref(outputs) if outputs is not None else None))
+
+    def step_pipelined(self, images_ptr, next_ptr, mem_kind, stride, image_stride, batch, params, outputs=None):
+        """next_ptr: host address of the FOLLOWING step's frames (copied during this step) or None."""
+        self._ck(self.lib.svo_gpu_step_pipelined(self.h, C.c_void_p(images_ptr), C.c_void_p(next_ptr) if next_ptr else None,
+                                                 mem_kind, stride, image_stride, batch, C.byref(params),
+                                                 C.byref(outputs) if outputs is not None else None))
 
     def step_reset(self):
         self._ck(self.lib.svo_gpu_step_reset(self.h))

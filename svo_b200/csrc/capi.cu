@@ -72,6 +72,11 @@ struct svo_gpu_ctx {
     int step_batch = 0;
     bool profile = false;
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    // frame ingest pipelining: the next step's host frames are copied on a second stream while this step computes
+    cudaStream_t copy_st = nullptr;
+    cudaEvent_t ev_copy = nullptr;
+    const uint8_t* pf_ptr = nullptr;   // host pointer of the prefetched frames (nullptr = none pending)
+    int pf_slot = -1;
     float stage_ms[4] = {0, 0, 0, 0};
 };
 
@@ -221,6 +226,8 @@ static int create_buffers(svo_gpu_ctx* ctx)
     }
     CK(cudaMallocHost(reinterpret_cast<void**>(&ctx->h_small), sizeof(int) * (4 * B + 16)));
     for (auto& e : ctx->ev) CK(cudaEventCreate(&e));
+    CK(cudaStreamCreateWithFlags(&ctx->copy_st, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&ctx->ev_copy, cudaEventDisableTiming));
     CK(cudaStreamSynchronize(ctx->st));
     return 0;
 }
@@ -267,6 +274,8 @@ extern "C" int svo_gpu_destroy(svo_gpu_ctx* ctx)
     if (!ctx) return 0;
     DeviceGuard guard(ctx->device);
     if (ctx->st) cudaStreamSynchronize(ctx->st);
+    if (ctx->copy_st) { cudaStreamSynchronize(ctx->copy_st); cudaStreamDestroy(ctx->copy_st); }
+    if (ctx->ev_copy) cudaEventDestroy(ctx->ev_copy);
     for (auto& s : ctx->slots) {
         cudaFree(s.raw_own.p);
         cudaFree(s.pyr.p);
@@ -285,10 +294,12 @@ extern "C" int svo_gpu_destroy(svo_gpu_ctx* ctx)
 }
 
 // ================================================================================================ images
-extern "C" int svo_gpu_upload_batch(svo_gpu_ctx* ctx, int slot, const uint8_t* images, int mem_kind, int w, int h,
-                                    size_t stride_bytes, size_t image_stride_bytes, int batch)
+// copies `batch` images into the slot on stream `cs` (enqueue only).  Host images that are tightly packed (stride == w,
+// images back to back) go over PCIe as ONE contiguous copy and stay compact on the device (row pitch w: the ingest kernel
+// reads any alignment); otherwise each image is a 2-D copy into 128 B-pitched rows.
+static int upload_to_slot(svo_gpu_ctx* ctx, int slot, const uint8_t* images, int mem_kind, int w, int h, size_t stride_bytes,
+                          size_t image_stride_bytes, int batch, cudaStream_t cs)
 {
-    if (!ctx) return SVO_GPU_E_ARG;
     if (int r = check_slot(ctx, slot)) return r;
     if (!images) return fail(ctx, SVO_GPU_E_ARG, "images is null");
     if (w < 1 || h < 1 || w > ctx->max_w || h > ctx->max_h)
@@ -297,28 +308,29 @@ extern "C" int svo_gpu_upload_batch(svo_gpu_ctx* ctx, int slot, const uint8_t* i
     if (stride_bytes < (size_t)w) return fail(ctx, SVO_GPU_E_ARG, "stride %zu < width %d", stride_bytes, w);
     if (batch > 1 && image_stride_bytes < stride_bytes * (size_t)h)
         return fail(ctx, SVO_GPU_E_ARG, "image stride smaller than one image");
-    DeviceGuard guard(ctx->device);
     Slot& s = ctx->slots[slot];
     if (mem_kind == SVO_GPU_MEM_DEVICE) {
         s.raw = images;   // aliased: the caller keeps it alive until the consuming calls have returned
         s.raw_pitch = stride_bytes;
         s.raw_lane = image_stride_bytes;
     } else if (mem_kind == SVO_GPU_MEM_HOST) {
-        const size_t pitch = round_up((size_t)w, 128);
-        const size_t lane = pitch * (size_t)h;
-        if (int r = ensure(ctx, s.raw_own, lane * (size_t)ctx->max_batch)) return r;
+        const size_t pitched = round_up((size_t)ctx->max_w, 128) * (size_t)ctx->max_h;
+        if (int r = ensure(ctx, s.raw_own, pitched * (size_t)ctx->max_batch + 64)) return r;
         uint8_t* d = static_cast<uint8_t*>(s.raw_own.p);
-        if (stride_bytes == (size_t)w && pitch == (size_t)w) {
-            for (int b = 0; b < batch; ++b)
-                CK(cudaMemcpyAsync(d + b * lane, images + b * image_stride_bytes, lane, cudaMemcpyHostToDevice, ctx->st));
+        const bool compact = stride_bytes == (size_t)w && (batch == 1 || image_stride_bytes == (size_t)w * h);
+        if (compact) {
+            CK(cudaMemcpyAsync(d, images, (size_t)w * h * batch, cudaMemcpyHostToDevice, cs));
+            s.raw_pitch = (size_t)w;
+            s.raw_lane = (size_t)w * h;
         } else {
+            const size_t pitch = round_up((size_t)w, 128), lane = pitch * (size_t)h;
             for (int b = 0; b < batch; ++b)
                 CK(cudaMemcpy2DAsync(d + b * lane, pitch, images + b * image_stride_bytes, stride_bytes, (size_t)w,
-                                     (size_t)h, cudaMemcpyHostToDevice, ctx->st));
+                                     (size_t)h, cudaMemcpyHostToDevice, cs));
+            s.raw_pitch = pitch;
+            s.raw_lane = lane;
         }
         s.raw = d;
-        s.raw_pitch = pitch;
-        s.raw_lane = lane;
     } else {
         return fail(ctx, SVO_GPU_E_ARG, "mem_kind %d unknown", mem_kind);
     }
@@ -326,6 +338,14 @@ extern "C" int svo_gpu_upload_batch(svo_gpu_ctx* ctx, int slot, const uint8_t* i
     s.uploaded = true;
     s.pyr_built = false;
     return 0;
+}
+
+extern "C" int svo_gpu_upload_batch(svo_gpu_ctx* ctx, int slot, const uint8_t* images, int mem_kind, int w, int h,
+                                    size_t stride_bytes, size_t image_stride_bytes, int batch)
+{
+    if (!ctx) return SVO_GPU_E_ARG;
+    DeviceGuard guard(ctx->device);
+    return upload_to_slot(ctx, slot, images, mem_kind, w, h, stride_bytes, image_stride_bytes, batch, ctx->st);
 }
 
 extern "C" int svo_gpu_upload(svo_gpu_ctx* ctx, int slot, const uint8_t* host, int w, int h, size_t stride_bytes)

@@ -101,15 +101,17 @@ __global__ void __launch_bounds__(256) fast_tile_kernel(const uint8_t* __restric
 
     // ---- stage the (TW+8) x (TH+8) region; coordinates are clamped to the image (clamped pixels are never used by a
     //      valid candidate: those sit at least 3 px inside the image)
-    const bool aligned = ((reinterpret_cast<uintptr_t>(src) | raw_pitch) & 3) == 0;
     for (int i = tid; i < RH * RWW; i += 256) {
         const int r = i / RWW, cw = i - r * RWW;
         const int gy = min(max(y0 - 4 + r, 0), h - 1);
         const int gx = x0 - 4 + cw * 4;
         const uint8_t* row = src + (size_t)gy * raw_pitch;
         uint32_t v;
-        if (aligned && gx >= 0 && gx + 3 < w) {
-            v = __ldg(reinterpret_cast<const uint32_t*>(row + gx));
+        if (gx >= 4 && gx + 7 < w) {
+            // two aligned words + funnel shift: any row pitch / alignment; the eight bytes read lie inside this row
+            const uintptr_t addr = reinterpret_cast<uintptr_t>(row + gx);
+            const uint32_t* wp = reinterpret_cast<const uint32_t*>(addr & ~(uintptr_t)3);
+            v = __funnelshift_r(__ldg(wp), __ldg(wp + 1), 8 * (int)(addr & 3));
         } else {
             v = 0;
 #pragma unroll

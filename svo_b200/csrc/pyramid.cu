@@ -25,14 +25,12 @@ __global__ void __launch_bounds__(128) ingest_kernel(const uint8_t* __restrict__
     const int sy = reflect101(py, L.h);
     const uint8_t* srow = raw + (size_t)lane * raw_lane + (size_t)sy * raw_pitch;
     uint32_t v;
-    if (px >= 0 && px + 3 < L.w) {
-        const uint8_t* p = srow + px;
-        if ((reinterpret_cast<uintptr_t>(p) & 3) == 0) {
-            v = __ldg(reinterpret_cast<const uint32_t*>(p));
-        } else {
-            v = (uint32_t)__ldg(p) | ((uint32_t)__ldg(p + 1) << 8) | ((uint32_t)__ldg(p + 2) << 16) |
-                ((uint32_t)__ldg(p + 3) << 24);
-        }
+    if (px >= 4 && px + 7 < L.w) {
+        // two aligned words + funnel shift: rows of any pitch / alignment (compact uploads have pitch = width); the eight
+        // bytes read lie inside this row
+        const uintptr_t addr = reinterpret_cast<uintptr_t>(srow + px);
+        const uint32_t* wp = reinterpret_cast<const uint32_t*>(addr & ~(uintptr_t)3);
+        v = __funnelshift_r(__ldg(wp), __ldg(wp + 1), 8 * (int)(addr & 3));
     } else {
         v = 0;
 #pragma unroll

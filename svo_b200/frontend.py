@@ -84,6 +84,11 @@ class Frontend:
         self.ctx.step(ptr, capi.MEM_HOST, stride, image_stride, self.batch, self.params,
                       self.out if with_outputs else None)
 
+    def step_host_pipelined(self, ptr, next_ptr, stride, image_stride, with_outputs=True):
+        """Like step_host_ptr, and starts the copy of the next step's frames (host address next_ptr, or None)."""
+        self.ctx.step_pipelined(ptr, next_ptr, capi.MEM_HOST, stride, image_stride, self.batch, self.params,
+                                self.out if with_outputs else None)
+
     def step_device(self, dev_ptr, stride, image_stride, with_outputs=False):
         """dev_ptr: device address of `batch` images (row pitch `stride`, image pitch `image_stride`)."""
         self.ctx.step(dev_ptr, capi.MEM_DEVICE, stride, image_stride, self.batch, self.params,

@@ -67,6 +67,32 @@ def test_step_device_memory_and_reset(oracle):
                     _check_lane(fe, b, cpus[b].step(seqs[b, t]), first=(t == 0))
 
 
+def test_step_pipelined_ingest(oracle):
+    """svo_gpu_step_pipelined: the next step's host frames are copied while this step computes; same answers, including
+    when a prefetch is not used (different pointer) and after a reset."""
+    import torch
+    from oracle.cpu_pipeline import CpuFrontend
+    seqs = _seqs(5)
+    B, T = seqs.shape[0], seqs.shape[1]
+    host = torch.from_numpy(np.ascontiguousarray(seqs.transpose(1, 0, 2, 3))).pin_memory()   # [t, lane, h, w]
+    other = host[2].clone().pin_memory()
+    with capi.Context(max_w=W, max_h=H, max_levels=4, max_points=8192, max_batch=B) as ctx:
+        fe = Frontend(ctx, W, H, B, kp_capacity=8192, bucket_capacity=2048, max_tracks=400)
+        for rep in range(2):
+            fe.reset()
+            cpus = [CpuFrontend(fe.pdict, impl="orc") for _ in range(B)]
+            for t in range(T):
+                nxt = host[t + 1].data_ptr() if t + 1 < T else None
+                cur = host[t].data_ptr()
+                if t == 1:
+                    nxt = host[4].data_ptr()          # a prefetch that the next call does not use
+                if t == 2:
+                    cur = other.data_ptr()            # same pixels as host[2], different pointer: copied normally
+                fe.step_host_pipelined(cur, nxt, W, W * H)
+                for b in range(B):
+                    _check_lane(fe, b, cpus[b].step(seqs[b, t]), first=(t == 0))
+
+
 def test_step_capacity_error():
     seqs = _seqs(1)
     with capi.Context(max_w=W, max_h=H, max_levels=4, max_points=8192, max_batch=3) as ctx:
