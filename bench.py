@@ -26,7 +26,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-from svo_b200 import synth  # noqa: E402
+from svo_b200 import sharding, synth  # noqa: E402
 
 RING = 8   # frames per stream kept resident; time stamps 0,1,2,3,4,3,2,1 so that consecutive frames (and the wrap) are ~2 px apart
 
@@ -44,14 +44,15 @@ def parse_args():
     return ap.parse_args()
 
 
-def make_frames(wl, streams, seed0):
-    """uint8 [RING, streams, h, w]: stream s = synthetic sequence with seed seed0 + s."""
+def make_frames(wl, streams, seed0, rank=0):
+    """uint8 [RING, streams, h, w]: stream s = synthetic sequence with seed sharding.stream_seeds(rank, streams, seed0)[s]."""
+    seeds = sharding.stream_seeds(rank, streams, seed0)
     w, h = wl["w"], wl["h"]
     times = synth.ring_times(RING)
     distinct = sorted(set(times))
 
     def one(s):
-        canvas = synth.make_canvas(w, h, seed0 + s)
+        canvas = synth.make_canvas(w, h, seeds[s])
         fr = {t: synth.render_frame(canvas, w, h, t) for t in distinct}
         return np.stack([fr[t] for t in times])
 
@@ -218,7 +219,7 @@ def run_b200(args):
     levels = wl["max_level"] + 1
     pitch = (w + 127) // 128 * 128
 
-    frames = make_frames(wl, S, wl["seed"] * 1000 + rank * S)            # [RING, S, h, w]
+    frames = make_frames(wl, S, wl["seed"] * 1000, rank)                  # [RING, S, h, w]
     dev = torch.zeros((RING, S, h, pitch), dtype=torch.uint8, device="cuda")
     dev[..., :w] = torch.from_numpy(frames).cuda()
     host = torch.from_numpy(frames).pin_memory()                         # compact rows, like a cv::Mat
@@ -237,11 +238,7 @@ def run_b200(args):
             dist.barrier()
 
     def max_over_ranks(ms):
-        if world == 1:
-            return ms
-        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+        return sharding.max_over_ranks(ms, world, device="cuda")
 
     # ---- end to end: host frames in, results out, every step.  svo_gpu_step_pipelined copies step i+1's frames (pinned host
     #      memory) on a second stream while step i computes; every step still waits for its own results on the host.
