@@ -54,6 +54,19 @@ def kernels():
     rows = list(csv.reader(raw.splitlines()))
     hdr, units = rows[0], rows[1]
     idx = {h: i for i, h in enumerate(hdr)}
+    # dram bytes per launch of each kernel family -> profiles/ncu_traffic.json (bench.py's roofline.traffic reads it)
+    fam = {"klt_kernel": "klt_run_kernel", "fast_kernel": "fast_tile_kernel", "pyrdown_kernel": "pyrdown_kernel",
+           "ingest_kernel": "ingest_kernel", "bucket_insert_kernel": "bucket_insert_kernel"}
+    tr = {"source": rep, "unit": "bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum)"}
+    mult = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    for key, pat in fam.items():
+        vals = [float(r[idx["dram__bytes_read.sum"]]) * mult[units[idx["dram__bytes_read.sum"]]] +
+                float(r[idx["dram__bytes_write.sum"]]) * mult[units[idx["dram__bytes_write.sum"]]]
+                for r in rows[2:] if pat in r[idx["Kernel Name"]]]
+        if vals:
+            tr[key] = max(vals)   # the level-0 launch for the per-level kernels
+    import json
+    json.dump(tr, open(os.path.join(os.path.dirname(dst), "ncu_traffic.json"), "w"), indent=1)
     with open(dst + "_kernels.txt", "w") as f:
         f.write("# ncu --set full --clock-control none; source: %s/prof.ncu-rep (one row block per captured launch)\n" % src)
         for r in rows[2:]:
