@@ -60,7 +60,9 @@ struct RunGeo {
     static constexpr int IROWS_ST = (IROWS + 32 / (RPI / 4) - 1) / (32 / (RPI / 4)) * (32 / (RPI / 4));
     static constexpr int REGION_WORDS = (IROWS_ST * RPI / 4 + 4 + 3) & ~3;
     static constexpr int PLANE_WORDS = (PROWS * BP + 8 + 3) & ~3;
-    static constexpr int WARP_WORDS = REGION_WORDS + PLANE_WORDS + JREGION_WORDS;
+    // border windows: packed (Ix | Iy << 16) of the few window pixels whose bilinear taps straddle the image edge
+    static constexpr int FIX_WORDS = (2 * (WW + WH) + 3) & ~3;   // left, right columns (by y), top, bottom rows (by x)
+    static constexpr int WARP_WORDS = REGION_WORDS + PLANE_WORDS + JREGION_WORDS + FIX_WORDS;
 };
 
 // The eight (byte i, byte i+1) pairs of a run, as DP2A operands: with w0 = bytes 0..3, w1 = 4..7, w2 = 8.. of the run,
@@ -285,98 +287,150 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) klt_run_kernel(const KltArgs
         // all derivative taps (ipx..ipx+WW, ipy..ipy+WH) inside the image?  (warp-uniform)
         const bool interior = ipx >= 0 && ipy >= 0 && ipx + WW < L.w && ipy + WH < L.h;
         int sA11 = 0, sA12 = 0, sA22 = 0;
-        if (interior) {
-            // ---- B(u,v) = unrounded bilinear sample of I at (ipx-1+u, ipy-1+v): plane run rb covers u = 8 seg .. 8 seg + 7
-            //      of row v, and sits at word 8 rb of the plane / byte 8 rb of the region (both pitches are 8 NSEGB)
-            {
-                const uint32_t wt = pack_weights(w.w00, w.w01), wb = pack_weights(w.w10, w.w11);
+        // ---- B(u,v) = unrounded bilinear sample of I at (ipx-1+u, ipy-1+v): plane run rb covers u = 8 seg .. 8 seg + 7
+        //      of row v, and sits at word 8 rb of the plane / byte 8 rb of the region (both pitches are 8 NSEGB)
+        {
+            const uint32_t wt = pack_weights(w.w00, w.w01), wb = pack_weights(w.w10, w.w11);
 #pragma unroll
-                for (int j = 0; j < G::RPLB; ++j) {
-                    const int rb = lane + 32 * j;
-                    if (rb < G::RUNSB) {
-                        const RunRow top = load_run_row(region_sa + 8 * rb), bot = load_run_row(region_sa + 8 * rb + G::RPI);
-                        int4 lo4, hi4;
-                        lo4.x = run_px<0>(top, bot, wt, wb, 0); lo4.y = run_px<1>(top, bot, wt, wb, 0);
-                        lo4.z = run_px<2>(top, bot, wt, wb, 0); lo4.w = run_px<3>(top, bot, wt, wb, 0);
-                        hi4.x = run_px<4>(top, bot, wt, wb, 0); hi4.y = run_px<5>(top, bot, wt, wb, 0);
-                        hi4.z = run_px<6>(top, bot, wt, wb, 0); hi4.w = run_px<7>(top, bot, wt, wb, 0);
-                        sts128(plane_sa + 32 * rb, lo4);
-                        sts128(plane_sa + 32 * rb + 16, hi4);
-                    }
+            for (int j = 0; j < G::RPLB; ++j) {
+                const int rb = lane + 32 * j;
+                if (rb < G::RUNSB) {
+                    const RunRow top = load_run_row(region_sa + 8 * rb), bot = load_run_row(region_sa + 8 * rb + G::RPI);
+                    int4 lo4, hi4;
+                    lo4.x = run_px<0>(top, bot, wt, wb, 0); lo4.y = run_px<1>(top, bot, wt, wb, 0);
+                    lo4.z = run_px<2>(top, bot, wt, wb, 0); lo4.w = run_px<3>(top, bot, wt, wb, 0);
+                    hi4.x = run_px<4>(top, bot, wt, wb, 0); hi4.y = run_px<5>(top, bot, wt, wb, 0);
+                    hi4.z = run_px<6>(top, bot, wt, wb, 0); hi4.w = run_px<7>(top, bot, wt, wb, 0);
+                    sts128(plane_sa + 32 * rb, lo4);
+                    sts128(plane_sa + 32 * rb + 16, hi4);
                 }
             }
+        }
+        // ---- Iw = DESCALE(B, 9);  Ixw = DESCALE(Scharr_x(B), 14);  Iyw = DESCALE(Scharr_y(B), 14)   (integer linearity)
+        //      separably: cs(u) = 3 B(u,v-1) + 10 B(u,v) + 3 B(u,v+1), rd(u) = B(u,v+1) - B(u,v-1);
+        //      Scharr_x = cs(u+1) - cs(u-1), Scharr_y = 3 rd(u-1) + 10 rd(u) + 3 rd(u+1)
+        auto derive_run = [&](int j, int* iv, int* ixv, int* iyv) {
+            int cs[10], rd[10], mid[10];
+            {
+                int r0[10], r2[10];
+                auto load10 = [](uint32_t sa, int* d) {
+                    const int4 x = lds128(sa), y = lds128(sa + 16);
+                    const uint2 z = lds64(sa + 32);
+                    d[0] = x.x; d[1] = x.y; d[2] = x.z; d[3] = x.w; d[4] = y.x; d[5] = y.y; d[6] = y.z; d[7] = y.w;
+                    d[8] = (int)z.x; d[9] = (int)z.y;
+                };
+                load10(po[j], r0);
+                load10(po[j] + 4 * BP, mid);
+                load10(po[j] + 8 * BP, r2);
+#pragma unroll
+                for (int u = 0; u < 10; ++u) {
+                    cs[u] = 3 * (r0[u] + r2[u]) + 10 * mid[u];
+                    rd[u] = r2[u] - r0[u];
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                iv[i] = descale(mid[i + 1], kWBits - 5);
+                ixv[i] = descale(cs[i + 2] - cs[i], kWBits);
+                iyv[i] = descale(3 * (rd[i] + rd[i + 2]) + 10 * rd[i + 1], kWBits);
+            }
+        };
+        if (interior) {
             __syncwarp();
-            // ---- Iw = DESCALE(B, 9);  Ixw = DESCALE(Scharr_x(B), 14);  Iyw = DESCALE(Scharr_y(B), 14)   (integer linearity)
-            //      separably: cs(u) = 3 B(u,v-1) + 10 B(u,v) + 3 B(u,v+1), rd(u) = B(u,v+1) - B(u,v-1);
-            //      Scharr_x = cs(u+1) - cs(u-1), Scharr_y = 3 rd(u-1) + 10 rd(u) + 3 rd(u+1)
 #pragma unroll
             for (int j = 0; j < RPL; ++j) {
-                int cs[10], rd[10], mid[10];
-                {
-                    int r0[10], r2[10];
-                    auto load10 = [](uint32_t sa, int* d) {
-                        const int4 x = lds128(sa), y = lds128(sa + 16);
-                        const uint2 z = lds64(sa + 32);
-                        d[0] = x.x; d[1] = x.y; d[2] = x.z; d[3] = x.w; d[4] = y.x; d[5] = y.y; d[6] = y.z; d[7] = y.w;
-                        d[8] = (int)z.x; d[9] = (int)z.y;
-                    };
-                    load10(po[j], r0);
-                    load10(po[j] + 4 * BP, mid);
-                    load10(po[j] + 8 * BP, r2);
-#pragma unroll
-                    for (int u = 0; u < 10; ++u) {
-                        cs[u] = 3 * (r0[u] + r2[u]) + 10 * mid[u];
-                        rd[u] = r2[u] - r0[u];
-                    }
-                }
+                int iv[8], ixv[8], iyv[8];
+                derive_run(j, iv, ixv, iyv);
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
-                    const int iv = descale(mid[i + 1], kWBits - 5);
-                    int ixv = descale(cs[i + 2] - cs[i], kWBits);
-                    int iyv = descale(3 * (rd[i] + rd[i + 2]) + 10 * rd[i + 1], kWBits);
-                    if (i >= nval[j]) { ixv = 0; iyv = 0; }
-                    set_px(j, i, iv, ixv, iyv);
-                    sA11 += ixv * ixv; sA12 += ixv * iyv; sA22 += iyv * iyv;
+                    if (i >= nval[j]) { ixv[i] = 0; iyv[i] = 0; }
+                    set_px(j, i, iv[i], ixv[i], iyv[i]);
+                    sA11 += ixv[i] * ixv[i]; sA12 += ixv[i] * iyv[i]; sA22 += iyv[i] * iyv[i];
                 }
             }
         } else {
-            // ---- border path: Scharr plane at (ipx..ipx+WW, ipy..ipy+WH), ZERO outside the image (calcScharrDeriv +
-            //      BORDER_CONSTANT), then bilinear on I, Ix, Iy exactly as OpenCV does
-            constexpr int dpitch = WW + 1;
-            constexpr int deriv_words = dpitch * (WH + 1);
-            for (int d = lane; d < deriv_words; d += 32) {
-                const int v = d / dpitch, u = d - v * dpitch;
-                const int X = ipx + u, Y = ipy + v;
-                uint32_t packed = 0;
-                if (X >= 0 && X < L.w && Y >= 0 && Y < L.h) {
-                    const uint8_t* r0 = rbytes + v * G::RPI + u;   // row Y-1, column X-1
-                    const uint8_t* r1 = r0 + G::RPI;
-                    const uint8_t* r2 = r1 + G::RPI;
-                    const int ix = 3 * ((int)r0[2] - (int)r0[0]) + 10 * ((int)r1[2] - (int)r1[0]) + 3 * ((int)r2[2] - (int)r2[0]);
-                    const int iy = 3 * ((int)r2[0] - (int)r0[0]) + 10 * ((int)r2[1] - (int)r0[1]) + 3 * ((int)r2[2] - (int)r0[2]);
-                    packed = ((uint32_t)ix & 0xffffu) | ((uint32_t)iy << 16);
-                }
-                plane[d] = (int)packed;
+            // ---- border window.  OpenCV's derivative image is ZERO outside the level (calcScharrDeriv writes the interior,
+            //      the winSize border is BORDER_CONSTANT) while the level itself is REFLECT_101-padded, so a window pixel at
+            //      image position (X, Y) has taps (X+i, Y+j), i, j in {0, 1}, of which only those inside the level count:
+            //        all four inside            -> the identity above holds (the margin of the stored level IS the
+            //                                      REFLECT_101 border calcScharrDeriv computes with)
+            //        none inside                -> Ix = Iy = 0
+            //        some inside ("straddling": X == -1, X == w-1, Y == -1 or Y == h-1; at most two columns and two rows
+            //                      of the window) -> the literal masked sum, computed here one pixel per lane into `fix`
+            const uint32_t fix_sa = jregion_sa + 4 * G::JREGION_WORDS;
+            const int xlo = max(0, -1 - ipx), xhi = min(WW, L.w - ipx);   // columns / rows with at least one tap inside
+            const int ylo = max(0, -1 - ipy), yhi = min(WH, L.h - ipy);
+            const int xsL = -1 - ipx, xsR = L.w - 1 - ipx, ysT = -1 - ipy, ysB = L.h - 1 - ipy;   // straddling ones
+            const bool hL = xsL >= 0 && xsL < WW, hR = xsR >= 0 && xsR < WW && xsR != xsL;
+            const bool hT = ysT >= 0 && ysT < WH, hB = ysB >= 0 && ysB < WH && ysB != ysT;
+            const int nL = hL ? WH : 0, nR = hR ? WH : 0, nT = hT ? WW : 0, nB = hB ? WW : 0;
+            const int nfix = nL + nR + nT + nB;
+            // list position k (compacted over the lists that exist) -> fixed slot: L at 0, R at WH, T at 2 WH, B at 2 WH + WW
+            auto k2slot = [&](int k) {
+                int t = k;
+                if (t < nL) return t;
+                if ((t -= nL) < nR) return WH + t;
+                if ((t -= nR) < nT) return 2 * WH + t;
+                return 2 * WH + WW + t - nT;
+            };
+            for (int k = lane; k < nfix; k += 32) {
+                int x, y, t = k;
+                if (t < nL) { x = xsL; y = t; }
+                else if ((t -= nL) < nR) { x = xsR; y = t; }
+                else if ((t -= nR) < nT) { x = t; y = ysT; }
+                else { x = t - nT; y = ysB; }
+                int ax = 0, ay = 0;
+#pragma unroll
+                for (int tj = 0; tj < 2; ++tj)
+#pragma unroll
+                    for (int ti = 0; ti < 2; ++ti) {
+                        const int X = ipx + x + ti, Y = ipy + y + tj;
+                        if (X >= 0 && X < L.w && Y >= 0 && Y < L.h) {
+                            const uint8_t* r0 = rbytes + (y + tj) * G::RPI + (x + ti);   // row Y-1, column X-1
+                            const uint8_t* r1 = r0 + G::RPI;
+                            const uint8_t* r2 = r1 + G::RPI;
+                            const int sx = 3 * ((int)r0[2] - (int)r0[0]) + 10 * ((int)r1[2] - (int)r1[0]) + 3 * ((int)r2[2] - (int)r2[0]);
+                            const int sy = 3 * ((int)r2[0] - (int)r0[0]) + 10 * ((int)r2[1] - (int)r0[1]) + 3 * ((int)r2[2] - (int)r0[2]);
+                            const int wk = tj ? (ti ? w.w11 : w.w10) : (ti ? w.w01 : w.w00);
+                            ax += sx * wk; ay += sy * wk;
+                        }
+                    }
+                sts32(fix_sa + 4 * k2slot(k), ((uint32_t)descale(ax, kWBits) & 0xffffu) | ((uint32_t)descale(ay, kWBits) << 16));
             }
             __syncwarp();
 #pragma unroll
             for (int j = 0; j < RPL; ++j) {
+                int iv[8], ixv[8], iyv[8];
+                derive_run(j, iv, ixv, iyv);
                 const int r = min(lane + 32 * j, G::RUNS - 1);
                 const int y = r / G::NSEG, x0 = 8 * (r - y * G::NSEG);
+                // bit i of zm: pixel i of the run has no tap inside (or is padding); of fm: it straddles -> take `fix`
+                const int lo = min(max(xlo - x0, 0), 8), hi = min(max(min(xhi, x0 + nval[j]) - x0, 0), 8);
+                unsigned keep = (y >= ylo && y < yhi) ? (((1u << hi) - 1u) & ~((1u << lo) - 1u)) : 0u;
+                unsigned fm = 0;
+                if ((hT && y == ysT) || (hB && y == ysB)) fm = keep;
+                else {
+                    if (hL && (unsigned)(xsL - x0) < 8u) fm |= 1u << (xsL - x0);
+                    if (hR && (unsigned)(xsR - x0) < 8u) fm |= 1u << (xsR - x0);
+                    fm &= keep;
+                }
+                if ((keep & ~fm) != 0xffu) {   // rare lanes: something to zero or to patch
+                    const bool rowT = hT && y == ysT, rowB = hB && y == ysB;
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        if (!((keep >> i) & 1u)) { ixv[i] = 0; iyv[i] = 0; }
+                        else if ((fm >> i) & 1u) {
+                            const int slot = rowT ? 2 * WH + x0 + i : rowB ? 2 * WH + WW + x0 + i : (x0 + i == xsL && hL) ? y : WH + y;
+                            const uint32_t v = lds32(fix_sa + 4 * slot);
+                            ixv[i] = (int)(short)(v & 0xffffu);
+                            iyv[i] = (int)v >> 16;
+                        }
+                    }
+                }
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
-                    int iv = 0, ixv = 0, iyv = 0;
-                    if (i < nval[j]) {
-                        const int x = x0 + i;
-                        iv = descale(bilin(rbytes + (y + 1) * G::RPI + x + 1, G::RPI, w), kWBits - 5);
-                        const int* dp = plane + y * dpitch + x;
-                        const int d00 = dp[0], d01 = dp[1], d10 = dp[dpitch], d11 = dp[dpitch + 1];
-                        ixv = descale((int)(short)(d00 & 0xffff) * w.w00 + (int)(short)(d01 & 0xffff) * w.w01 +
-                                          (int)(short)(d10 & 0xffff) * w.w10 + (int)(short)(d11 & 0xffff) * w.w11, kWBits);
-                        iyv = descale((d00 >> 16) * w.w00 + (d01 >> 16) * w.w01 + (d10 >> 16) * w.w10 + (d11 >> 16) * w.w11, kWBits);
-                    }
-                    set_px(j, i, iv, ixv, iyv);
-                    sA11 += ixv * ixv; sA12 += ixv * iyv; sA22 += iyv * iyv;
+                    set_px(j, i, iv[i], ixv[i], iyv[i]);
+                    sA11 += ixv[i] * ixv[i]; sA12 += ixv[i] * iyv[i]; sA22 += iyv[i] * iyv[i];
                 }
             }
         }
