@@ -131,6 +131,51 @@ SVO_GPU_API int svo_gpu_klt(svo_gpu_ctx* ctx, int slot_prev, int slot_next, cons
 /* total LK iterations executed by the last svo_gpu_klt / step call (all lanes), for the op model of the roofline */
 SVO_GPU_API long long svo_gpu_last_klt_iterations(svo_gpu_ctx* ctx);
 
+/* ---------------------------------------------------------------------------------------------- filters ------- */
+
+/* The loops that follow each LK call in the reference, as an order-preserving compaction on the device:
+ *   y_threshold <  0: keep i iff status[i]                                              (src/tracking.cpp:168-175)
+ *   y_threshold >= 0: keep i iff status[i] && std::abs(b[i].y - a[i].y) < y_threshold    (src/tracking.cpp:109-115)
+ * Survivors keep their input order; index_out[k] is the input position of survivor k (so that the caller can carry
+ * Feature::mapPoint over, src/tracking.cpp:112,171).  index_out / a_out / b_out may be NULL; capacity is theirs. */
+SVO_GPU_API int svo_gpu_filter_tracks(svo_gpu_ctx* ctx, const float* a_xy, const float* b_xy, const uint8_t* status, int n,
+                                      float y_threshold, int* index_out, float* a_out, float* b_out, int capacity,
+                                      int* n_out);
+
+/* Tracking::trackFrames (src/tracking.cpp:154-179) in one call on lane 0: LK from slot_prev to slot_next on prev_xy,
+ * then the status filter, chained on the device; only the survivors are copied back.
+ *   index_out[k] = position in prev_xy of survivor k, curr_out = its tracked position, err_out = its LK err (or NULL). */
+SVO_GPU_API int svo_gpu_track_frames(svo_gpu_ctx* ctx, int slot_prev, int slot_next, const float* prev_xy, int n, int win_w,
+                                     int win_h, int max_level, int max_count, double epsilon, int criteria_type, int flags,
+                                     double min_eig_threshold, int* index_out, float* curr_out, float* err_out,
+                                     int capacity, int* n_out);
+
+/* Parameters of Tracking::extractFeatures + findLeftFeaturesInRight (src/tracking.cpp:74-122). */
+typedef struct svo_gpu_keyframe_params {
+    int fast_threshold;     /* include/config_reader.h:36 (20) */
+    int fast_nms;           /* include/config_reader.h:37 (true) */
+    float mask_half;        /* src/tracking.cpp:78 (10); <= 0 disables the mask */
+    int bucket_size;        /* <= 0: no bucketing (the reference as shipped, "todo" at src/tracking.cpp:88) */
+    int per_bucket;
+    int win_w, win_h;       /* src/tracking.cpp:104 (11, 11) */
+    int max_level;          /* src/tracking.cpp:104 (3) */
+    int max_count;          /* src/tracking.cpp:98 (30) */
+    double epsilon;         /* src/tracking.cpp:98 (0.001) */
+    int criteria_type;      /* COUNT + EPS */
+    int flags;              /* 0 */
+    double min_eig_threshold;
+    float y_threshold;      /* include/config_reader.h:41 (40); < 0 disables the epipolar test */
+} svo_gpu_keyframe_params;
+
+/* A key-frame's feature extraction in one call on lane 0, everything chained on the device:
+ * mask around prev_xy (:76-79) -> FAST on slot_left (:82) -> optional bucketing (:88) -> LK from slot_left to
+ * slot_right on the detections (:101-105) -> status / epipolar filter (:109-115).  Both slots need pyramids built with a
+ * window >= (win_w, win_h).  Outputs: left_out / right_out = surviving stereo pairs in detection order,
+ * *n_detected = detections LK ran on, *n_out = pairs kept. */
+SVO_GPU_API int svo_gpu_keyframe(svo_gpu_ctx* ctx, int slot_left, int slot_right, const float* prev_xy, int n_prev,
+                                 const svo_gpu_keyframe_params* params, float* left_out, float* right_out, int capacity,
+                                 int* n_detected, int* n_out);
+
 /* ---------------------------------------------------------------------------------------------- per-frame step - */
 
 /* Parameters of one front-end frame, i.e. what Tracking::startStereo does per key-frame (src/tracking.cpp:240-257):

@@ -43,6 +43,13 @@ SYMBOLS = {
     "svo_gpu_klt": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
                               C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, C.c_double]),
     "svo_gpu_last_klt_iterations": (C.c_longlong, [C.c_void_p]),
+    "svo_gpu_filter_tracks": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_void_p,
+                                        C.c_void_p, C.c_void_p, C.c_int, _i32p]),
+    "svo_gpu_track_frames": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
+                                       C.c_int, C.c_double, C.c_int, C.c_int, C.c_double, C.c_void_p, C.c_void_p,
+                                       C.c_void_p, C.c_int, _i32p]),
+    "svo_gpu_keyframe": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                   C.c_int, _i32p, _i32p]),
     "svo_gpu_step": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_size_t, C.c_size_t, C.c_int, C.c_void_p,
                                C.c_void_p]),
     "svo_gpu_step_pipelined": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_size_t, C.c_size_t, C.c_int,
@@ -60,6 +67,14 @@ class StepParams(C.Structure):
                 ("win_w", C.c_int), ("win_h", C.c_int), ("max_level", C.c_int), ("max_count", C.c_int),
                 ("epsilon", C.c_double), ("criteria_type", C.c_int), ("flags", C.c_int),
                 ("min_eig_threshold", C.c_double)]
+
+
+class KeyframeParams(C.Structure):
+    """struct svo_gpu_keyframe_params"""
+    _fields_ = [("fast_threshold", C.c_int), ("fast_nms", C.c_int), ("mask_half", C.c_float), ("bucket_size", C.c_int),
+                ("per_bucket", C.c_int), ("win_w", C.c_int), ("win_h", C.c_int), ("max_level", C.c_int),
+                ("max_count", C.c_int), ("epsilon", C.c_double), ("criteria_type", C.c_int), ("flags", C.c_int),
+                ("min_eig_threshold", C.c_double), ("y_threshold", C.c_float)]
 
 
 class StepOutputs(C.Structure):
@@ -221,6 +236,52 @@ class Context:
                                       win[1], max_level, max_count, float(epsilon), criteria_type, flags,
                                       float(min_eig_threshold)))
         return nxy[:n], st[:n], er[:n]
+
+    # ------------------------------------------------------------------ filters and fused call chains
+    def filter_tracks(self, a_xy, b_xy, status, y_threshold=-1.0):
+        """src/tracking.cpp:168-175 (y_threshold < 0) / :109-115 -> (index, a, b) of the survivors, input order kept."""
+        a = np.ascontiguousarray(a_xy, np.float32).reshape(-1, 2)
+        b = np.ascontiguousarray(b_xy, np.float32).reshape(-1, 2)
+        st = np.ascontiguousarray(status, np.uint8).reshape(-1)
+        n = len(a)
+        assert len(b) == n and len(st) == n
+        idx = np.zeros(max(n, 1), np.int32)
+        ao = np.zeros((max(n, 1), 2), np.float32)
+        bo = np.zeros((max(n, 1), 2), np.float32)
+        m = C.c_int(0)
+        self._ck(self.lib.svo_gpu_filter_tracks(self.h, _ptr(a), _ptr(b), _ptr(st), n, float(y_threshold), _ptr(idx),
+                                                _ptr(ao), _ptr(bo), n, C.byref(m)))
+        return idx[:m.value].copy(), ao[:m.value].copy(), bo[:m.value].copy()
+
+    def track_frames(self, slot_prev, slot_next, prev_xy, win=(21, 21), max_level=3, max_count=50, epsilon=0.001,
+                     criteria_type=TC_COUNT | TC_EPS, flags=LK_GET_MIN_EIGENVALS, min_eig_threshold=1e-4):
+        """Tracking::trackFrames (src/tracking.cpp:154-179): LK + status filter -> (index, curr_xy, err) of the survivors."""
+        pxy = np.ascontiguousarray(prev_xy, np.float32).reshape(-1, 2)
+        n = len(pxy)
+        idx = np.zeros(max(n, 1), np.int32)
+        cur = np.zeros((max(n, 1), 2), np.float32)
+        er = np.zeros(max(n, 1), np.float32)
+        m = C.c_int(0)
+        self._ck(self.lib.svo_gpu_track_frames(self.h, slot_prev, slot_next, _ptr(pxy), n, win[0], win[1], max_level,
+                                               max_count, float(epsilon), criteria_type, flags, float(min_eig_threshold),
+                                               _ptr(idx), _ptr(cur), _ptr(er), n, C.byref(m)))
+        return idx[:m.value].copy(), cur[:m.value].copy(), er[:m.value].copy()
+
+    def keyframe(self, slot_left, slot_right, prev_xy, fast_threshold=20, fast_nms=True, mask_half=10.0, bucket_size=0,
+                 per_bucket=0, win=(11, 11), max_level=3, max_count=30, epsilon=0.001, criteria_type=TC_COUNT | TC_EPS,
+                 flags=0, min_eig_threshold=1e-4, y_threshold=40.0, capacity=None):
+        """Tracking::extractFeatures + findLeftFeaturesInRight (src/tracking.cpp:74-122) -> (left, right, n_detected)."""
+        pxy = np.ascontiguousarray(prev_xy, np.float32).reshape(-1, 2)
+        cap = self.max_points if capacity is None else capacity
+        P = KeyframeParams(int(fast_threshold), int(bool(fast_nms)), float(mask_half), int(bucket_size), int(per_bucket),
+                           win[0], win[1], max_level, max_count, float(epsilon), criteria_type, flags,
+                           float(min_eig_threshold), float(y_threshold))
+        lo = np.zeros((max(cap, 1), 2), np.float32)
+        ro = np.zeros((max(cap, 1), 2), np.float32)
+        nd, m = C.c_int(0), C.c_int(0)
+        self._ck(self.lib.svo_gpu_keyframe(self.h, slot_left, slot_right, _ptr(pxy) if len(pxy) else None, len(pxy),
+                                           C.byref(P), _ptr(lo), _ptr(ro), cap, C.byref(nd), C.byref(m)))
+        return lo[:m.value].copy(), ro[:m.value].copy(), nd.value
 
     @property
     def last_klt_iterations(self):

@@ -62,6 +62,12 @@ struct svo_gpu_ctx {
     int* int_max = nullptr;       // [B] all INT_MAX: "n is given by n_max" for the host-pointer calls
     unsigned long long* d_iters = nullptr;
     long long last_iters = 0;
+    // status / epipolar filter outputs (filter.cu)
+    int* flt_index = nullptr;     // [B][max_points]
+    float2* flt_a = nullptr;
+    float2* flt_b = nullptr;
+    float* flt_err = nullptr;
+    int* flt_n = nullptr;         // [B]
     // pinned scratch for small read-backs
     int* h_small = nullptr;       // 4 * max_batch + 16 ints
 
@@ -218,6 +224,11 @@ static int create_buffers(svo_gpu_ctx* ctx)
     if (int r = dmalloc(ctx, ctx->trk_n, B)) return r;
     if (int r = dmalloc(ctx, ctx->int_max, B)) return r;
     if (int r = dmalloc(ctx, ctx->d_iters, 1)) return r;
+    if (int r = dmalloc(ctx, ctx->flt_index, B * NP)) return r;
+    if (int r = dmalloc(ctx, ctx->flt_a, B * NP)) return r;
+    if (int r = dmalloc(ctx, ctx->flt_b, B * NP)) return r;
+    if (int r = dmalloc(ctx, ctx->flt_err, B * NP)) return r;
+    if (int r = dmalloc(ctx, ctx->flt_n, B)) return r;
     CK(cudaMemsetAsync(ctx->trk_n, 0, sizeof(int) * B, ctx->st));
     CK(cudaMemsetAsync(ctx->d_iters, 0, sizeof(unsigned long long), ctx->st));
     {
@@ -283,7 +294,8 @@ extern "C" int svo_gpu_destroy(svo_gpu_ctx* ctx)
     void* bufs[] = {ctx->fb.rowtotal, ctx->fb.segcnt, ctx->fb.segkp, ctx->fb.kp_xy, ctx->fb.kp_resp, ctx->fb.kp_count,
                     ctx->mask.p, ctx->bb.out_xy, ctx->bb.out_age, ctx->bb.out_count, ctx->bb.err_flag, ctx->cell_slots.p,
                     ctx->cell_cnt.p, ctx->cell_last.p, ctx->bk_in_xy, ctx->bk_in_age, ctx->trk_xy, ctx->nxt_xy,
-                    ctx->trk_status, ctx->trk_err, ctx->trk_n, ctx->int_max, ctx->d_iters};
+                    ctx->trk_status, ctx->trk_err, ctx->trk_n, ctx->int_max, ctx->d_iters, ctx->flt_index, ctx->flt_a,
+                    ctx->flt_b, ctx->flt_err, ctx->flt_n};
     for (void* p : bufs) cudaFree(p);
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
     for (auto& e : ctx->ev)
@@ -406,4 +418,5 @@ extern "C" int svo_gpu_download_level(svo_gpu_ctx* ctx, int slot, int lane, int 
 }
 
 #include "capi_ops.inc"
+#include "capi_fused.inc"
 #include "capi_step.inc"

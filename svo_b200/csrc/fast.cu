@@ -321,8 +321,8 @@ void launch_build_mask(cudaStream_t st, uint8_t* mask, size_t mask_pitch, size_t
                        const float2* pts, size_t pts_lane, const int* n_dev, int n_max, float half, int batch,
                        long long* launches)
 {
-    for (int b = 0; b < batch; ++b)
-        cudaMemset2DAsync(mask + (size_t)b * mask_lane, mask_pitch, 255, (size_t)w, (size_t)h, st);
+    // one fill for all lanes (lanes are mask_lane apart and the padding of a lane is never read)
+    cudaMemsetAsync(mask, 255, (size_t)(batch - 1) * mask_lane + (size_t)(h - 1) * mask_pitch + (size_t)w, st);
     if (n_max <= 0) return;
     mask_boxes_kernel<<<dim3((n_max + 3) / 4, batch), 128, 0, st>>>(mask, mask_pitch, mask_lane, w, h, pts, pts_lane,
                                                                   n_dev, n_max, half);

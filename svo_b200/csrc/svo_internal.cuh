@@ -112,4 +112,24 @@ struct KltArgs {
 };
 void launch_klt(cudaStream_t st, const KltArgs& a, int batch, long long* launches);
 
+// ------------------------------------------------------------------------------------------------ filter.cu
+struct FilterArgs {
+    const float2* a_xy;        // [B][pts_lane] points LK started from (left / previous)
+    const float2* b_xy;        // [B][pts_lane] points LK found (right / current)
+    const uint8_t* status;     // [B][pts_lane]
+    size_t pts_lane;
+    const int* n_dev;          // [B] list length per lane (device), clamped to n_max
+    int n_max;
+    int use_y;                 // 1: also require |b.y - a.y| < y_threshold (src/tracking.cpp:110)
+    float y_threshold;
+    const float* err;          // [B][pts_lane] LK err (may be null)
+    float* out_err;            // [B][pts_lane] err of each survivor (may be null)
+    int* out_index;            // [B][pts_lane] input position of each survivor (may be null)
+    float2* out_a;             // [B][pts_lane] (may be null)
+    float2* out_b;             // [B][pts_lane] (may be null)
+    int out_cap;
+    int* out_n;                // [B] survivors per lane
+};
+void launch_filter(cudaStream_t st, const FilterArgs& a, int batch, long long* launches);
+
 }  // namespace svo

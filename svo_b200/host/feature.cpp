@@ -176,4 +176,93 @@ void calcOpticalFlowPyrLK(const cv::Mat& prevImg, const cv::Mat& nextImg, const 
     if (rc != SVO_GPU_OK) raise(ctx, "svo_gpu_klt", rc);
 }
 
+// ------------------------------------------------------------------------------------------------ fused chains
+namespace {
+
+void upload_pair(svo_gpu_ctx* ctx, const cv::Mat& a, const cv::Mat& b, int win, int max_level)
+{
+    int rc;
+    if ((rc = svo_gpu_upload(ctx, 0, a.data, a.cols, a.rows, a.step)) || (rc = svo_gpu_upload(ctx, 1, b.data, b.cols, b.rows, b.step)))
+        raise(ctx, "svo_gpu_upload", rc);
+    if ((rc = svo_gpu_build_pyramid(ctx, 0, win, win, max_level, nullptr)) || (rc = svo_gpu_build_pyramid(ctx, 1, win, win, max_level, nullptr)))
+        raise(ctx, "svo_gpu_build_pyramid", rc);
+}
+
+void check_pair(const cv::Mat& a, const cv::Mat& b, const char* who)
+{
+    check_image(a, who);
+    check_image(b, who);
+    if (a.empty() || a.rows != b.rows || a.cols != b.cols)
+        throw cv::Exception(std::string(who) + ": the two images must be non-empty and of the same size");
+}
+
+}  // namespace
+
+void trackFrames(const cv::Mat& prevImg, const cv::Mat& currImg, const std::vector<cv::Point2f>& prevPts,
+                 std::vector<cv::Point2f>& currPts, std::vector<int>& indices)
+{
+    const int n = (int)prevPts.size();
+    currPts.clear();
+    indices.clear();
+    if (n == 0) return;
+    check_pair(prevImg, currImg, "trackFrames");
+    svo_gpu_ctx* ctx = defaultContext(g_tab.device, prevImg.cols, prevImg.rows, n);
+    upload_pair(ctx, prevImg, currImg, 21, 3);
+    currPts.resize((size_t)n);
+    indices.resize((size_t)n);
+    int m = 0;
+    const int rc = svo_gpu_track_frames(ctx, 0, 1, reinterpret_cast<const float*>(prevPts.data()), n, 21, 21, 3, 50, 0.001,
+                                        SVO_GPU_TC_COUNT | SVO_GPU_TC_EPS, SVO_GPU_LK_GET_MIN_EIGENVALS, 1e-4, indices.data(),
+                                        reinterpret_cast<float*>(currPts.data()), nullptr, n, &m);
+    if (rc != SVO_GPU_OK) raise(ctx, "svo_gpu_track_frames", rc);
+    currPts.resize((size_t)m);
+    indices.resize((size_t)m);
+}
+
+void extractStereoFeatures(const cv::Mat& leftImg, const cv::Mat& rightImg, const std::vector<cv::Point2f>& tracked,
+                           int threshold, bool nms, float yThreshold, std::vector<cv::Point2f>& leftPts,
+                           std::vector<cv::Point2f>& rightPts, int bucketSize, int featuresPerBucket)
+{
+    check_pair(leftImg, rightImg, "extractStereoFeatures");
+    // every pixel can be a keypoint without NMS; with it at most one in four
+    const int cap = std::max(4096, leftImg.rows * leftImg.cols / 4);
+    svo_gpu_ctx* ctx = defaultContext(g_tab.device, leftImg.cols, leftImg.rows, std::max(cap, (int)tracked.size()));
+    upload_pair(ctx, leftImg, rightImg, 11, 3);
+    svo_gpu_keyframe_params P{};
+    P.fast_threshold = threshold; P.fast_nms = nms ? 1 : 0; P.mask_half = 10.f;
+    P.bucket_size = bucketSize; P.per_bucket = featuresPerBucket;
+    P.win_w = 11; P.win_h = 11; P.max_level = 3; P.max_count = 30; P.epsilon = 0.001;
+    P.criteria_type = SVO_GPU_TC_COUNT | SVO_GPU_TC_EPS; P.flags = 0; P.min_eig_threshold = 1e-4;
+    P.y_threshold = yThreshold;
+    leftPts.resize((size_t)cap);
+    rightPts.resize((size_t)cap);
+    int nd = 0, m = 0;
+    const int rc = svo_gpu_keyframe(ctx, 0, 1, tracked.empty() ? nullptr : reinterpret_cast<const float*>(tracked.data()),
+                                    (int)tracked.size(), &P, reinterpret_cast<float*>(leftPts.data()),
+                                    reinterpret_cast<float*>(rightPts.data()), cap, &nd, &m);
+    if (rc != SVO_GPU_OK) {
+        leftPts.clear();
+        rightPts.clear();
+        raise(ctx, "svo_gpu_keyframe", rc);
+    }
+    leftPts.resize((size_t)m);
+    rightPts.resize((size_t)m);
+}
+
+void filterTracks(const std::vector<cv::Point2f>& a, const std::vector<cv::Point2f>& b, const std::vector<uchar>& status,
+                  float yThreshold, std::vector<int>& indices)
+{
+    const int n = (int)a.size();
+    if (b.size() != a.size() || status.size() != a.size()) throw cv::Exception("filterTracks: a, b and status differ in length");
+    indices.clear();
+    if (n == 0) return;
+    svo_gpu_ctx* ctx = defaultContext(g_tab.device, 0, 0, n);
+    indices.resize((size_t)n);
+    int m = 0;
+    const int rc = svo_gpu_filter_tracks(ctx, reinterpret_cast<const float*>(a.data()), reinterpret_cast<const float*>(b.data()),
+                                         status.data(), n, yThreshold, indices.data(), nullptr, nullptr, n, &m);
+    if (rc != SVO_GPU_OK) raise(ctx, "svo_gpu_filter_tracks", rc);
+    indices.resize((size_t)m);
+}
+
 }  // namespace svo

@@ -96,6 +96,19 @@ int main(int argc, char** argv)
             put(fo, status.data(), status.size());
             put(fo, error.data, 4 * (size_t)error.rows);
         }
+        // ---- the fused chains: trackFrames (:154-179) and extractFeatures + findLeftFeaturesInRight (:74-122, y_threshold 0.9)
+        {
+            std::vector<cv::Point2f> cur, lp, rp;
+            std::vector<int> idx;
+            svo::trackFrames(a, b, fs.points, cur, idx);
+            put_i(fo, (int)cur.size());
+            put(fo, idx.data(), 4 * idx.size());
+            put(fo, cur.data(), 8 * cur.size());
+            svo::extractStereoFeatures(a, b, prevPts, 20, true, 0.9f, lp, rp);
+            put_i(fo, (int)lp.size());
+            put(fo, lp.data(), 8 * lp.size());
+            put(fo, rp.data(), 8 * rp.size());
+        }
         // ---- empty inputs behave like OpenCV
         std::vector<cv::Point2f> none, out;
         std::vector<uchar> st;

@@ -81,4 +81,25 @@ void calcOpticalFlowPyrLK(const cv::Mat& prevImg, const cv::Mat& nextImg, const 
                           cv::TermCriteria criteria = cv::TermCriteria(cv::TermCriteria::COUNT + cv::TermCriteria::EPS, 30, 0.01),
                           int flags = 0, double minEigThreshold = 1e-4);
 
+
+// ---- the reference's call chains with their filter loops, fused on the device ----------------
+
+// Tracking::trackFrames (src/tracking.cpp:154-179): LK 21x21 / maxLevel 3 / {COUNT+EPS, 50, 0.001} /
+// OPTFLOW_LK_GET_MIN_EIGENVALS from prevImg to currImg, then `if (status[i])`.  currPts = positions of the surviving
+// tracks in input order, indices[k] = position in prevPts of survivor k (to carry Feature::mapPoint over, :171).
+void trackFrames(const cv::Mat& prevImg, const cv::Mat& currImg, const std::vector<cv::Point2f>& prevPts,
+                 std::vector<cv::Point2f>& currPts, std::vector<int>& indices);
+
+// Tracking::extractFeatures + findLeftFeaturesInRight (src/tracking.cpp:74-122): mask around `tracked` (+-10 px), FAST
+// (threshold, nms) on leftImg, optional bucketing (bucketSize > 0: the "todo" of :88), LK 11x11 / maxLevel 3 /
+// {COUNT+EPS, 30, 0.001} into rightImg, then `status[i] && std::abs(right.y - left.y) < yThreshold`.
+// leftPts / rightPts = the surviving stereo pairs in detection order.
+void extractStereoFeatures(const cv::Mat& leftImg, const cv::Mat& rightImg, const std::vector<cv::Point2f>& tracked,
+                           int threshold, bool nms, float yThreshold, std::vector<cv::Point2f>& leftPts,
+                           std::vector<cv::Point2f>& rightPts, int bucketSize = 0, int featuresPerBucket = 0);
+
+// The filter loop alone (src/tracking.cpp:109-115; yThreshold < 0: :168-175) for callers that ran LK themselves.
+void filterTracks(const std::vector<cv::Point2f>& a, const std::vector<cv::Point2f>& b, const std::vector<uchar>& status,
+                  float yThreshold, std::vector<int>& indices);
+
 }  // namespace svo

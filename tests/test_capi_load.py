@@ -37,6 +37,10 @@ def test_struct_layouts_match_header():
     assert C.sizeof(capi.StepParams) == 72
     assert capi.StepParams.epsilon.offset == 48 and capi.StepParams.min_eig_threshold.offset == 64
     assert C.sizeof(capi.StepOutputs) == 96
+    # svo_gpu_keyframe_params: 9 ints/floats, pad, double, 2 ints, double, float, pad
+    assert C.sizeof(capi.KeyframeParams) == 72
+    assert capi.KeyframeParams.epsilon.offset == 40 and capi.KeyframeParams.min_eig_threshold.offset == 56
+    assert capi.KeyframeParams.y_threshold.offset == 64
 
 
 def test_create_without_gpu_fails_loudly(lib):
@@ -51,4 +55,6 @@ def test_create_without_gpu_fails_loudly(lib):
 def test_null_context_is_rejected(lib):
     assert lib.svo_gpu_upload(None, 0, None, 1, 1, 1) == capi.E_ARG
     assert lib.svo_gpu_step_reset(None) == capi.E_ARG
+    assert lib.svo_gpu_filter_tracks(None, None, None, None, 0, -1.0, None, None, None, 0, None) == capi.E_ARG
+    assert lib.svo_gpu_keyframe(None, 0, 1, None, 0, None, None, None, 0, None, None) == capi.E_ARG
     assert lib.svo_gpu_destroy(None) == 0

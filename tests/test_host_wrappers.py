@@ -87,5 +87,18 @@ def test_wrappers_match_oracle(exe, oracle, tmp_path):
         er = take(np.float32, n)
         oxy2, ost, oer = oracle.orc_klt(a, b, bxy, **mode)
         assert np.array_equal(st, ost) and np.array_equal(nxy, oxy2) and np.array_equal(er, oer)
+    # fused chains: trackFrames on the bucketed points, extractStereoFeatures with y_threshold 0.9
+    m = int(take(np.int32, 1)[0])
+    idx = take(np.int32, m)
+    cur = take(np.float32, 2 * m).reshape(m, 2)
+    oxy2, ost, _ = oracle.orc_klt(a, b, bxy, win=(21, 21), max_level=3, max_count=50, epsilon=0.001, flags=8)
+    keep = np.nonzero(ost)[0]
+    assert np.array_equal(idx, keep) and np.array_equal(cur, oxy2[keep])
+    m = int(take(np.int32, 1)[0])
+    lp = take(np.float32, 2 * m).reshape(m, 2)
+    rp = take(np.float32, 2 * m).reshape(m, 2)
+    rxy, rst, _ = oracle.orc_klt(a, b, oxy, win=(11, 11), max_level=3, max_count=30, epsilon=0.001, flags=0)
+    keep = np.nonzero((rst != 0) & (np.abs(rxy[:, 1] - oxy[:, 1]) < np.float32(0.9)))[0]
+    assert m == len(keep) and np.array_equal(lp, oxy[keep]) and np.array_equal(rp, rxy[keep])
     assert int(take(np.int32, 1)[0]) == 0                    # empty inputs -> empty outputs, like OpenCV
     assert off == len(buf)
