@@ -43,12 +43,14 @@ struct RunGeo {
     // next-image region: the (WW+1) x (WH+1) window plus a margin of MJ pixels on every side, staged UNSHIFTED (word
     // aligned) once per level; the Newton iterations move the window inside it and only re-stage when they leave it
     static constexpr int MJ = 3;
-    static constexpr int PJ0 = (WW + 1 + 3 + 2 * MJ + 3) & ~3;
-    static constexpr int PJ = (PJ0 / 4) % 2 == 0 ? PJ0 + 4 : PJ0;   // bytes per row; an odd word count spreads the banks
-    static constexpr int DXMAX = PJ - 1 - WW, DYMAX = 2 * MJ;       // legal window offsets inside the region
-    static constexpr int OWJ = PJ / 4, RPPJ = 32 / OWJ;
-    static constexpr int PASSJ = (WH + 1 + 2 * MJ + RPPJ - 1) / RPPJ;
-    static constexpr int JREGION_WORDS = (PASSJ * RPPJ * OWJ + 4 + 3) & ~3;
+    // region rows start at a 16-byte boundary of the image row (16-byte cp.async), so the window's first column sits
+    // MJ .. MJ + 15 bytes into a region row; a run reads three whole words from the word holding its first byte
+    static constexpr int PJ = (((2 * MJ + 15) & ~3) + 8 * (NSEG - 1) + 12 + 15) & ~15;   // bytes per region row
+    static constexpr int DXMAX = PJ - 8 * (NSEG - 1) - 12 + 3, DYMAX = 2 * MJ;           // legal window offsets
+    static constexpr int JROWS = WH + 1 + 2 * MJ;
+    static constexpr int CPR = PJ / 16, JCHUNKS = JROWS * CPR;                           // 16-byte chunks
+    static constexpr int PASSJ = (JCHUNKS + 31) / 32;
+    static constexpr int JREGION_WORDS = JROWS * PJ / 4 + 4;
     static constexpr int NSEGB = (WW + 2) / 8 + 1;     // runs per row of the B plane (WW + 2 values per row)
     static constexpr int RPI = 8 * NSEGB;              // bytes per staged row of the previous image (needs WW + 3)
     static constexpr int IROWS = WH + 3;
@@ -124,9 +126,9 @@ __device__ __forceinline__ RunRow load_run_row_unaligned(uint32_t addr, int sh)
     return r;
 }
 
-__device__ __forceinline__ void cp_async4(uint32_t dst, const void* src)
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src)
 {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
 }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
@@ -196,13 +198,21 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) klt_run_kernel(const KltArgs
     const uint8_t* rbytes = reinterpret_cast<const uint8_t*>(region);
 
     // ---- per-lane constants: staging maps, and for each owned run its offsets and number of valid pixels
-    constexpr int OWI = G::RPI / 4, OWJ = G::OWJ;
+    constexpr int OWI = G::RPI / 4;
     const uint32_t region_sa = (uint32_t)__cvta_generic_to_shared(region);   // 32-bit shared-window addresses
     const uint32_t plane_sa = (uint32_t)__cvta_generic_to_shared(plane);
     const int sI_r = min(lane / OWI, 32 / OWI - 1), sI_c = lane % OWI;       // staging maps: lane -> (row, word) of a pass;
-    const int sJ_r = min(lane / OWJ, G::RPPJ - 1), sJ_c = lane % OWJ;        // spare lanes repeat a word of the last row
+                                                                             // spare lanes repeat a word of the last row
     const uint32_t jregion_sa = plane_sa + 4 * G::PLANE_WORDS;
-    const uint32_t sI_dst = region_sa + 4 * (sI_r * OWI + sI_c), sJ_dst = jregion_sa + 4 * (sJ_r * OWJ + sJ_c);
+    const uint32_t sI_dst = region_sa + 4 * (sI_r * OWI + sI_c);
+    // next-image region: lane -> 16-byte chunk (row, column) of each pass; chunks past the end repeat the last one
+    int sJ_row[G::PASSJ], sJ_col16[G::PASSJ];
+#pragma unroll
+    for (int k = 0; k < G::PASSJ; ++k) {
+        const int c = min(lane + 32 * k, G::JCHUNKS - 1);
+        sJ_row[k] = c / G::CPR;
+        sJ_col16[k] = 16 * (c - sJ_row[k] * G::CPR);
+    }
     uint32_t jo[RPL], po[RPL];
     int nval[RPL];
 #pragma unroll
@@ -261,12 +271,12 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) klt_run_kernel(const KltArgs
         int sx0 = 0, sy0 = 0;      // image coordinates of region byte (0, 0)
         bool jstaged = false;
         auto stage_j = [&](int inx, int iny) {
-            sx0 = (inx - G::MJ) & ~3;
+            sx0 = (inx - G::MJ) & ~15;
             sy0 = iny - G::MJ;
-            const uint8_t* src = Jorigin + (long long)(sy0 + sJ_r) * L.pitch + (sx0 + 4 * sJ_c);
+            const uint8_t* src = Jorigin + (long long)sy0 * L.pitch + sx0;
 #pragma unroll
             for (int k = 0; k < G::PASSJ; ++k)
-                cp_async4(sJ_dst + k * G::RPPJ * G::PJ, src + (long long)(k * G::RPPJ) * L.pitch);
+                cp_async16(jregion_sa + sJ_row[k] * G::PJ + sJ_col16[k], src + (sJ_row[k] * L.pitch + sJ_col16[k]));
             jstaged = true;
         };
         cp_async_wait_all();   // a copy started at a level that was then skipped may still be in flight
@@ -549,13 +559,13 @@ void launch_run(cudaStream_t st, const KltArgs& a, int batch)
 
 // tuning knobs of the 21x21 instantiation (warps per CTA, packed gradients, minimum CTAs per SM -> register cap)
 #ifndef KLT21_WARPS
-#define KLT21_WARPS 4
+#define KLT21_WARPS 1   // one track per CTA: a slot is refilled as soon as its track converges (no intra-CTA tail)
 #endif
 #ifndef KLT21_PACKG
 #define KLT21_PACKG false
 #endif
 #ifndef KLT21_MINB
-#define KLT21_MINB 5
+#define KLT21_MINB 20
 #endif
 
 }  // namespace
@@ -564,8 +574,8 @@ void launch_klt(cudaStream_t st, const KltArgs& a, int batch, long long* launche
 {
     if (a.n_max <= 0) return;
     if (a.win_w == 21 && a.win_h == 21) launch_run<21, 21, KLT21_WARPS, KLT21_PACKG, KLT21_MINB>(st, a, batch);
-    else if (a.win_w == 11 && a.win_h == 11) launch_run<11, 11, 8, false, 2>(st, a, batch);
-    else if (a.win_w == 31 && a.win_h == 31) launch_run<31, 31, 4, true, 1>(st, a, batch);
+    else if (a.win_w == 11 && a.win_h == 11) launch_run<11, 11, 1, false, 16>(st, a, batch);
+    else if (a.win_w == 31 && a.win_h == 31) launch_run<31, 31, 1, true, 8>(st, a, batch);
     else launch_klt_generic(st, a, batch);
     if (launches) ++*launches;
 }
