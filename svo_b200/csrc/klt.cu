@@ -43,18 +43,27 @@ struct RunGeo {
     // next-image region: the (WW+1) x (WH+1) window plus a margin of MJ pixels on every side, staged UNSHIFTED (word
     // aligned) once per level; the Newton iterations move the window inside it and only re-stage when they leave it
     static constexpr int MJ = 3;
-    // region rows start at a 16-byte boundary of the image row (16-byte cp.async), so the window's first column sits
-    // MJ .. MJ + 15 bytes into a region row; a run reads three whole words from the word holding its first byte
-    static constexpr int PJ = (((2 * MJ + 15) & ~3) + 8 * (NSEG - 1) + 12 + 15) & ~15;   // bytes per region row
-    static constexpr int DXMAX = PJ - 8 * (NSEG - 1) - 12 + 3, DYMAX = 2 * MJ;           // legal window offsets
+    // region rows start at a word boundary of the image row, so the window's first column sits MJ .. MJ + 3 bytes into a
+    // region row; a run reads three whole words from the word holding its first byte.  OWJ words of every row are copied;
+    // rows are PJW words apart, PJW picked (by enumeration) so that the lanes' 32-bit loads of one instruction -- word
+    // index PJW y + 2 seg for the run (y, seg) -- spread over the banks: 21x21 3 wavefronts for the two rounds of 32 runs
+    // (a 12-word pitch needs 6), 11x11 1, 31x31 8 for four rounds
+    static constexpr int OWJ = ((2 * MJ + 3) & ~3) / 4 + 2 * (NSEG - 1) + 3;
+    static constexpr int PJW = NSEG == 3 ? 19 : NSEG == 2 ? 9 : NSEG == 4 ? 13 : (OWJ | 1);
+    static_assert(PJW >= OWJ, "row pitch shorter than the copied words");
+    static constexpr int PJ = 4 * PJW;                                  // bytes per region row
+    static constexpr int DXMAX = 4 * OWJ - 1 - WW, DYMAX = 2 * MJ;      // legal window offsets inside the region
     static constexpr int JROWS = WH + 1 + 2 * MJ;
-    static constexpr int CPR = PJ / 16, JCHUNKS = JROWS * CPR;                           // 16-byte chunks
-    static constexpr int PASSJ = (JCHUNKS + 31) / 32;
-    static constexpr int JREGION_WORDS = JROWS * PJ / 4 + 4;
+    static constexpr int RPPJ = 32 / OWJ;                               // rows per staging pass
+    static constexpr int PASSJ = (JROWS + RPPJ - 1) / RPPJ;
+    static constexpr int JREGION_WORDS = (PASSJ * RPPJ * PJW + 4 + 3) & ~3;
     static constexpr int NSEGB = (WW + 2) / 8 + 1;     // runs per row of the B plane (WW + 2 values per row)
     static constexpr int RPI = 8 * NSEGB;              // bytes per staged row of the previous image (needs WW + 3)
     static constexpr int IROWS = WH + 3;
-    static constexpr int BP = 8 * NSEGB;               // plane pitch in words
+    // a plane run (8 values) occupies a block of 12 words: lanes 48 bytes apart make every 128-bit access of a warp
+    // conflict-free (8 consecutive lanes cover the 32 banks), where 32-byte blocks would only ever touch half the banks
+    static constexpr int BBLK = 12;
+    static constexpr int BP = BBLK * NSEGB;            // plane pitch in words
     static constexpr int PROWS = WH + 2;
     static constexpr int RUNSB = PROWS * NSEGB;
     static constexpr int RPLB = (RUNSB + 31) / 32;
@@ -126,9 +135,9 @@ __device__ __forceinline__ RunRow load_run_row_unaligned(uint32_t addr, int sh)
     return r;
 }
 
-__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src)
+__device__ __forceinline__ void cp_async4(uint32_t dst, const void* src)
 {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
 }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
@@ -205,14 +214,9 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) klt_run_kernel(const KltArgs
                                                                              // spare lanes repeat a word of the last row
     const uint32_t jregion_sa = plane_sa + 4 * G::PLANE_WORDS;
     const uint32_t sI_dst = region_sa + 4 * (sI_r * OWI + sI_c);
-    // next-image region: lane -> 16-byte chunk (row, column) of each pass; chunks past the end repeat the last one
-    int sJ_row[G::PASSJ], sJ_col16[G::PASSJ];
-#pragma unroll
-    for (int k = 0; k < G::PASSJ; ++k) {
-        const int c = min(lane + 32 * k, G::JCHUNKS - 1);
-        sJ_row[k] = c / G::CPR;
-        sJ_col16[k] = 16 * (c - sJ_row[k] * G::CPR);
-    }
+    // next-image region: lane -> (row, word) of a staging pass; spare lanes repeat a word of the pass's last row
+    const int sJ_r = min(lane / G::OWJ, G::RPPJ - 1), sJ_c = lane % G::OWJ;
+    const uint32_t sJ_dst = jregion_sa + 4 * (sJ_r * G::PJW + sJ_c);
     uint32_t jo[RPL], po[RPL];
     int nval[RPL];
 #pragma unroll
@@ -221,7 +225,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) klt_run_kernel(const KltArgs
         const int rr = min(r, G::RUNS - 1);
         const int y = rr / G::NSEG, seg = rr - y * G::NSEG;
         jo[j] = jregion_sa + y * G::PJ + 8 * seg;    // shared address of the run when the window sits at (0, 0) of the region
-        po[j] = plane_sa + 4 * (y * BP + 8 * seg);   // shared address of plane element (x, y), x = the run's first pixel
+        po[j] = plane_sa + 4 * (y * BP + G::BBLK * seg);   // shared address of plane element (x, y), x = the run's first pixel
         nval[j] = r < G::RUNS ? min(8, WW - 8 * seg) : 0;
     }
 
@@ -271,12 +275,12 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) klt_run_kernel(const KltArgs
         int sx0 = 0, sy0 = 0;      // image coordinates of region byte (0, 0)
         bool jstaged = false;
         auto stage_j = [&](int inx, int iny) {
-            sx0 = (inx - G::MJ) & ~15;
+            sx0 = (inx - G::MJ) & ~3;
             sy0 = iny - G::MJ;
-            const uint8_t* src = Jorigin + (long long)sy0 * L.pitch + sx0;
+            const uint8_t* src = Jorigin + (long long)(sy0 + sJ_r) * L.pitch + (sx0 + 4 * sJ_c);
 #pragma unroll
             for (int k = 0; k < G::PASSJ; ++k)
-                cp_async16(jregion_sa + sJ_row[k] * G::PJ + sJ_col16[k], src + (sJ_row[k] * L.pitch + sJ_col16[k]));
+                cp_async4(sJ_dst + k * G::RPPJ * G::PJ, src + (long long)(k * G::RPPJ) * L.pitch);
             jstaged = true;
         };
         cp_async_wait_all();   // a copy started at a level that was then skipped may still be in flight
@@ -298,7 +302,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) klt_run_kernel(const KltArgs
         const bool interior = ipx >= 0 && ipy >= 0 && ipx + WW < L.w && ipy + WH < L.h;
         int sA11 = 0, sA12 = 0, sA22 = 0;
         // ---- B(u,v) = unrounded bilinear sample of I at (ipx-1+u, ipy-1+v): plane run rb covers u = 8 seg .. 8 seg + 7
-        //      of row v, and sits at word 8 rb of the plane / byte 8 rb of the region (both pitches are 8 NSEGB)
+        //      of row v, and sits in block rb of the plane (BBLK words each) / at byte 8 rb of the region (NSEGB runs per row)
         {
             const uint32_t wt = pack_weights(w.w00, w.w01), wb = pack_weights(w.w10, w.w11);
 #pragma unroll
@@ -311,8 +315,8 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) klt_run_kernel(const KltArgs
                     lo4.z = run_px<2>(top, bot, wt, wb, 0); lo4.w = run_px<3>(top, bot, wt, wb, 0);
                     hi4.x = run_px<4>(top, bot, wt, wb, 0); hi4.y = run_px<5>(top, bot, wt, wb, 0);
                     hi4.z = run_px<6>(top, bot, wt, wb, 0); hi4.w = run_px<7>(top, bot, wt, wb, 0);
-                    sts128(plane_sa + 32 * rb, lo4);
-                    sts128(plane_sa + 32 * rb + 16, hi4);
+                    sts128(plane_sa + 4 * G::BBLK * rb, lo4);
+                    sts128(plane_sa + 4 * G::BBLK * rb + 16, hi4);
                 }
             }
         }
@@ -325,7 +329,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) klt_run_kernel(const KltArgs
                 int r0[10], r2[10];
                 auto load10 = [](uint32_t sa, int* d) {
                     const int4 x = lds128(sa), y = lds128(sa + 16);
-                    const uint2 z = lds64(sa + 32);
+                    const uint2 z = lds64(sa + 4 * G::BBLK);   // values 8, 9 open the next block
                     d[0] = x.x; d[1] = x.y; d[2] = x.z; d[3] = x.w; d[4] = y.x; d[5] = y.y; d[6] = y.z; d[7] = y.w;
                     d[8] = (int)z.x; d[9] = (int)z.y;
                 };
