@@ -88,6 +88,10 @@ SVO_GPU_API int svo_gpu_build_pyramid(svo_gpu_ctx* ctx, int slot, int win_w, int
 /* Test/debug read-back of one pyramid level of lane `lane` (tightly packed w*h bytes). */
 SVO_GPU_API int svo_gpu_download_level(svo_gpu_ctx* ctx, int slot, int lane, int level, uint8_t* host, int capacity_bytes,
                                        int* w_out, int* h_out);
+/* The same level WITH its BORDER_REFLECT_101 margin, as cv::buildOpticalFlowPyramid stores it (the margin here is
+ * *margin_out >= the window it was built for): host receives (h + 2 margin) rows of (w + 2 margin) bytes. */
+SVO_GPU_API int svo_gpu_download_level_padded(svo_gpu_ctx* ctx, int slot, int lane, int level, uint8_t* host,
+                                              int capacity_bytes, int* w_out, int* h_out, int* margin_out);
 
 /* ---------------------------------------------------------------------------------------------- FAST ---------- */
 

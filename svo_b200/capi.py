@@ -34,6 +34,8 @@ SYMBOLS = {
                                        C.c_size_t, C.c_int]),
     "svo_gpu_build_pyramid": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, _i32p]),
     "svo_gpu_download_level": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, _i32p, _i32p]),
+    "svo_gpu_download_level_padded": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, _i32p, _i32p,
+                                                _i32p]),
     "svo_gpu_fast": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p,
                                C.c_int, _i32p]),
     "svo_gpu_fast_masked_by_points": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_float,
@@ -182,6 +184,17 @@ class Context:
         out = np.empty((h.value, w.value), np.uint8)
         self._ck(self.lib.svo_gpu_download_level(self.h, slot, lane, level, _ptr(out), out.size, C.byref(w), C.byref(h)))
         return out
+
+    def download_level_padded(self, slot, level, lane=0):
+        """Level with its REFLECT_101 margin -> (array (h + 2m, w + 2m), m)."""
+        w, h, m = C.c_int(0), C.c_int(0), C.c_int(0)
+        rc = self.lib.svo_gpu_download_level_padded(self.h, slot, lane, level, None, 0, C.byref(w), C.byref(h), C.byref(m))
+        if rc not in (0, E_CAPACITY):
+            self._ck(rc)
+        out = np.empty((h.value + 2 * m.value, w.value + 2 * m.value), np.uint8)
+        self._ck(self.lib.svo_gpu_download_level_padded(self.h, slot, lane, level, _ptr(out), out.size, C.byref(w),
+                                                        C.byref(h), C.byref(m)))
+        return out, m.value
 
     # ------------------------------------------------------------------ FAST
     def fast(self, slot, threshold=20, nms=True, mask=None, capacity=None):

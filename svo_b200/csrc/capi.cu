@@ -417,6 +417,28 @@ extern "C" int svo_gpu_download_level(svo_gpu_ctx* ctx, int slot, int lane, int 
     return 0;
 }
 
+extern "C" int svo_gpu_download_level_padded(svo_gpu_ctx* ctx, int slot, int lane, int level, uint8_t* host,
+                                             int capacity_bytes, int* w_out, int* h_out, int* margin_out)
+{
+    if (!ctx) return SVO_GPU_E_ARG;
+    if (int r = check_slot(ctx, slot)) return r;
+    Slot& s = ctx->slots[slot];
+    if (!s.pyr_built) return fail(ctx, SVO_GPU_E_STATE, "pyramid of slot %d not built", slot);
+    if (level < 0 || level >= s.g.nlevels || lane < 0 || lane >= s.batch)
+        return fail(ctx, SVO_GPU_E_ARG, "level %d / lane %d out of range", level, lane);
+    const LevelGeom& L = s.g.lv[level];
+    const int P = s.g.P, pw = L.w + 2 * P, ph = L.h + 2 * P;
+    if (w_out) *w_out = L.w;
+    if (h_out) *h_out = L.h;
+    if (margin_out) *margin_out = P;
+    if (!host || capacity_bytes < pw * ph) return fail(ctx, SVO_GPU_E_CAPACITY, "need %d bytes", pw * ph);
+    DeviceGuard guard(ctx->device);
+    const uint8_t* src = static_cast<const uint8_t*>(s.pyr.p) + (size_t)lane * s.g.lane_bytes + L.off - (long long)P * L.pitch - P;
+    CK(cudaMemcpy2DAsync(host, (size_t)pw, src, (size_t)L.pitch, (size_t)pw, (size_t)ph, cudaMemcpyDeviceToHost, ctx->st));
+    CK(cudaStreamSynchronize(ctx->st));
+    return 0;
+}
+
 #include "capi_ops.inc"
 #include "capi_fused.inc"
 #include "capi_step.inc"

@@ -4,8 +4,8 @@
 // cv::calcOpticalFlowPyrLK runs on both images at every call (reference call sites src/tracking.cpp:101-105, :160-165):
 //   level l = pyrDown(level l-1):  dst(x,y) = (sum_{i,j=-2..2} w_i w_j src(R(2x+i), R(2y+j)) + 128) >> 8, w = [1 4 6 4 1],
 //   R = BORDER_REFLECT_101, dst size ((w+1)/2, (h+1)/2); every level carries a REFLECT_101 margin.
-// HBM-bound streaming stencils: each thread produces 4 output bytes from aligned 32-bit loads; because the source level
-// already carries its reflected margin, no thread needs border logic for its reads.
+// HBM-bound streaming stencils: each thread produces 4 output bytes from aligned word loads, once, and scatters them to
+// the margin positions that reflect onto them.
 #include "svo_internal.cuh"
 
 namespace svo {
@@ -41,68 +41,91 @@ __global__ void __launch_bounds__(128) ingest_kernel(const uint8_t* __restrict__
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// level l-1 -> level l, margins included.  One thread = 4 consecutive dst pixels of one padded dst row.
-// Interior quads read 5 rows x 16 source bytes as aligned words; the margin quads (left/right only: rows are handled by
-// reflecting the row index) fall back to per-pixel reflected reads.
-// grid = (ceil((dw+2P)/4 / 128), dh+2P, batch)
+// level l-1 -> level l.  One thread = 4 consecutive dst pixels of one dst row, each output computed ONCE: the thread then
+// also stores its pixels at every margin position that BORDER_REFLECT_101 maps onto them (rows: the same quad, aligned;
+// columns: mirrored, byte by byte), so the level leaves the kernel with its complete margin and the next level -- and LK --
+// read it without border logic.  The source level carries its own margin (ingest / the previous launch), hence no thread
+// needs border logic for its reads either: 5 rows x 16 bytes as aligned 32/64-bit loads, and the separable [1 4 6 4 1]
+// filter as DP4A: the horizontal taps of output k sit in two ALIGNED words, so with the vertical weight folded in
+//   out0 = w0 . (0,0,1,4)K + w1 . (6,4,1,0)K     out1 = w1 . (1,4,6,4)K + w2 . (1,0,0,0)K
+//   out2 = w1 . (0,0,1,4)K + w2 . (6,4,1,0)K     out3 = w2 . (1,4,6,4)K + w3 . (1,0,0,0)K      (K = 1, 4, 6, 4, 1 per row)
+// i.e. 8 DP4A per source row and no shifts or byte extraction.
+// grid = (ceil(ceil(dw/4) / 128), dh, batch)
 // ---------------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ int pyr_px(const uint8_t* __restrict__ s, int pitch, int cx, int cy)
+// smallest value >= lo that is congruent to v modulo period
+__device__ __forceinline__ int first_at_least(int v, int period, int lo)
 {
-    // 5x5 around (cx, cy) in a padded source level (margin >= 2 guaranteed)
-    const int K[5] = {1, 4, 6, 4, 1};
-    int acc = 0;
-#pragma unroll
-    for (int j = 0; j < 5; ++j) {
-        const uint8_t* r = s + (long long)(cy + j - 2) * pitch + cx - 2;
-        int hsum = (int)r[0] + 4 * (int)r[1] + 6 * (int)r[2] + 4 * (int)r[3] + (int)r[4];
-        acc += K[j] * hsum;
-    }
-    return (acc + 128) >> 8;
+    int m = (v - lo) % period;
+    if (m < 0) m += period;
+    return lo + m;
+}
+
+__device__ __forceinline__ uint32_t pack4(uint32_t a, uint32_t b, uint32_t c, uint32_t d)
+{
+    return a | (b << 8) | (c << 16) | (d << 24);
 }
 
 __global__ void __launch_bounds__(128) pyrdown_kernel(uint8_t* __restrict__ pyr, long long lane_bytes, LevelGeom S,
                                                       LevelGeom D, int P)
 {
-    const int q = blockIdx.x * blockDim.x + threadIdx.x;
-    const int px = q * 4 - P;
-    if (px >= D.w + P) return;
-    const int py = (int)blockIdx.y - P;
-    const int lane = blockIdx.z;
-    uint8_t* base = pyr + (size_t)lane * lane_bytes;
-    const uint8_t* s = base + S.off;
-    const int ry = reflect101(py, D.h);
-    uint32_t out;
-    if (px >= 0 && px + 3 < D.w) {
-        // source columns 2px-4 .. 2px+11 (aligned words), rows 2ry-2 .. 2ry+2
-        int acc0 = 0, acc1 = 0, acc2 = 0, acc3 = 0;
-        const int K[5] = {1, 4, 6, 4, 1};
+    const int px = 4 * (blockIdx.x * blockDim.x + threadIdx.x);
+    if (px >= D.w) return;
+    const int py = blockIdx.y;
+    uint8_t* base = pyr + (size_t)blockIdx.z * lane_bytes;
+    // source columns 2px-4 .. 2px+11 (bytes 2..12 are used), rows 2py-2 .. 2py+2; 2px-4 is 4 mod 8: one 32-bit, one 64-bit,
+    // one 32-bit load per row
+    uint32_t acc0 = 128, acc1 = 128, acc2 = 128, acc3 = 128;
+    const uint8_t* r0 = base + S.off + (long long)(2 * py - 2) * S.pitch + 2 * px - 4;
 #pragma unroll
-        for (int j = 0; j < 5; ++j) {
-            const uint32_t* r =
-                reinterpret_cast<const uint32_t*>(s + (long long)(2 * ry + j - 2) * S.pitch + 2 * px - 4);
-            const uint32_t w0 = r[0], w1 = r[1], w2 = r[2], w3 = r[3];
-            // bytes b[i] = column 2px-4+i
-            const int b2 = (w0 >> 16) & 255, b3 = w0 >> 24;
-            const int b4 = w1 & 255, b5 = (w1 >> 8) & 255, b6 = (w1 >> 16) & 255, b7 = w1 >> 24;
-            const int b8 = w2 & 255, b9 = (w2 >> 8) & 255, b10 = (w2 >> 16) & 255, b11 = w2 >> 24;
-            const int b12 = w3 & 255;
-            acc0 += K[j] * (b2 + 4 * b3 + 6 * b4 + 4 * b5 + b6);
-            acc1 += K[j] * (b4 + 4 * b5 + 6 * b6 + 4 * b7 + b8);
-            acc2 += K[j] * (b6 + 4 * b7 + 6 * b8 + 4 * b9 + b10);
-            acc3 += K[j] * (b8 + 4 * b9 + 6 * b10 + 4 * b11 + b12);
-        }
-        out = (uint32_t)((acc0 + 128) >> 8) | ((uint32_t)((acc1 + 128) >> 8) << 8) |
-              ((uint32_t)((acc2 + 128) >> 8) << 16) | ((uint32_t)((acc3 + 128) >> 8) << 24);
-    } else {
-        out = 0;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const int rx = reflect101(px + i, D.w);
-            out |= (uint32_t)pyr_px(s, S.pitch, 2 * rx, 2 * ry) << (8 * i);
+    for (int j = 0; j < 5; ++j) {
+        const uint32_t k = j == 0 || j == 4 ? 1 : j == 2 ? 6 : 4;
+        const uint8_t* r = r0 + (long long)j * S.pitch;
+        const uint2 mid = __ldg(reinterpret_cast<const uint2*>(r + 4));
+        const uint32_t w0 = __ldg(reinterpret_cast<const uint32_t*>(r)), w1 = mid.x, w2 = mid.y;
+        const uint32_t w3 = __ldg(reinterpret_cast<const uint32_t*>(r + 12));
+        const uint32_t A = (k << 16) | ((4 * k) << 24);                            // (0, 0, 1, 4) k
+        const uint32_t B = (6 * k) | ((4 * k) << 8) | (k << 16);                   // (6, 4, 1, 0) k
+        const uint32_t Cw = k | ((4 * k) << 8) | ((6 * k) << 16) | ((4 * k) << 24);   // (1, 4, 6, 4) k
+        const uint32_t E = k;                                                      // (1, 0, 0, 0) k
+        acc0 = __dp4a(w0, A, acc0); acc0 = __dp4a(w1, B, acc0);
+        acc1 = __dp4a(w1, Cw, acc1); acc1 = __dp4a(w2, E, acc1);
+        acc2 = __dp4a(w1, A, acc2); acc2 = __dp4a(w2, B, acc2);
+        acc3 = __dp4a(w2, Cw, acc3); acc3 = __dp4a(w3, E, acc3);
+    }
+    const uint32_t out = pack4(acc0 >> 8, acc1 >> 8, acc2 >> 8, acc3 >> 8);
+    const int nv = min(4, D.w - px);                    // valid pixels of the quad (the rest would be margin positions)
+
+    uint8_t* lv = base + D.off;
+    // does any pixel of the quad have mirror images among the margin columns?  (x <= P on the left, x >= w-1-P on the right)
+    const bool colwork = px <= P || px + nv - 1 >= D.w - 1 - P;
+    const int perh = 2 * D.h - 2, perw = 2 * D.w - 2;   // periods of the reflection (levels are larger than 1 x 1)
+    // all rows t in [-P, h+P) with reflect101(t) == py: t = +-py + k perh
+#pragma unroll 1
+    for (int sgn = 0; sgn < 2; ++sgn) {
+        if (sgn == 1 && (py == 0 || py == D.h - 1)) break;          // -py is the same residue as py
+        int t = sgn ? -py : py;
+        t = first_at_least(t, perh, -P);
+#pragma unroll 1
+        for (; t < D.h + P; t += perh) {
+            uint8_t* drow = lv + (long long)t * D.pitch;
+            if (nv == 4) *reinterpret_cast<uint32_t*>(drow + px) = out;
+            else
+                for (int i = 0; i < nv; ++i) drow[px + i] = (uint8_t)(out >> (8 * i));
+            if (colwork) {
+                for (int i = 0; i < nv; ++i) {
+                    const int x = px + i;
+                    const uint8_t v = (uint8_t)(out >> (8 * i));
+                    for (int sg = 0; sg < 2; ++sg) {
+                        if (sg == 1 && (x == 0 || x == D.w - 1)) break;
+                        int c = sg ? -x : x;
+                        c = first_at_least(c, perw, -P);
+                        for (; c < D.w + P; c += perw)
+                            if (c != x) drow[c] = v;
+                    }
+                }
+            }
         }
     }
-    uint8_t* drow = base + D.off + (long long)py * D.pitch;
-    *reinterpret_cast<uint32_t*>(drow + px) = out;
 }
 
 void launch_ingest(cudaStream_t st, const uint8_t* raw, size_t raw_pitch, size_t raw_lane, uint8_t* pyr,
@@ -119,8 +142,8 @@ void launch_pyrdown(cudaStream_t st, uint8_t* pyr, const PyrGeom& g, int level, 
 {
     const LevelGeom& S = g.lv[level - 1];
     const LevelGeom& D = g.lv[level];
-    const int quads = (D.w + 2 * g.P + 3) / 4;
-    dim3 grid((quads + 127) / 128, D.h + 2 * g.P, batch);
+    const int quads = (D.w + 3) / 4;
+    dim3 grid((quads + 127) / 128, D.h, batch);
     pyrdown_kernel<<<grid, 128, 0, st>>>(pyr, g.lane_bytes, S, D, g.P);
     if (launches) ++*launches;
 }

@@ -23,6 +23,18 @@ def ctx():
     c.close()
 
 
+def _reflect_pad(a, m):
+    """BORDER_REFLECT_101 by m pixels, also when m exceeds the image size (index map applied repeatedly, as OpenCV does)."""
+    def idx(n):
+        i = np.arange(-m, n + m)
+        if n == 1:
+            return np.zeros_like(i)
+        period = 2 * n - 2
+        i = np.mod(i, period)
+        return np.where(i >= n, period - i, i)
+    return a[np.ix_(idx(a.shape[0]), idx(a.shape[1]))]
+
+
 # ------------------------------------------------------------------------------------------------ FAST
 def _images():
     canvas = synth.make_canvas(1241, 376, 11)
@@ -99,6 +111,9 @@ def test_pyramid_bit_exact(ctx, oracle, shape):
         assert levels == len(ref) - 1
         for l in range(levels + 1):
             assert np.array_equal(ctx.download_level(1, l), ref[l]), (shape, win, l)
+            padded, m = ctx.download_level_padded(1, l)      # the BORDER_REFLECT_101 margin LK reads
+            assert m >= max(win)
+            assert np.array_equal(padded, _reflect_pad(ref[l], m)), (shape, win, l)
 
 
 # ------------------------------------------------------------------------------------------------ bucketing
