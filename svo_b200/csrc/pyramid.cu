@@ -6,38 +6,66 @@
 //   R = BORDER_REFLECT_101, dst size ((w+1)/2, (h+1)/2); every level carries a REFLECT_101 margin.
 // HBM-bound streaming stencils: each thread produces 4 output bytes from aligned word loads, once, and scatters them to
 // the margin positions that reflect onto them.
+#include <algorithm>
+
 #include "svo_internal.cuh"
 
 namespace svo {
 
 // ---------------------------------------------------------------------------------------------------------------
-// raw -> padded level 0.  One thread = 4 consecutive bytes of one padded row (one aligned 32-bit store).
-// grid = (ceil((w+2P)/4 / 128), h+2P, batch)
+// raw -> padded level 0, in 16-byte chunks of a padded row (one aligned 128-bit store each; the margin is a multiple of 16, so
+// chunk boundaries fall on column 0).  Chunks whose 16 + 4 source bytes lie inside the raw row are copied by
+// ingest_kernel: five aligned words + four funnel shifts, rows of any pitch / alignment (compact uploads have pitch = w).
+// The few chunks per row that touch the left / right margin go to ingest_edge_kernel, whose warps hold 32 consecutive ROWS
+// of one edge chunk, so that the per-byte BORDER_REFLECT_101 path never shares a warp with the streaming path.
+// grid = (ceil(nfast / 128), h+2P, batch)  and  (ceil((h+2P) / 128), nedge, batch)
 // ---------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128) ingest_kernel(const uint8_t* __restrict__ raw, size_t raw_pitch, size_t raw_lane,
-                                                     uint8_t* __restrict__ pyr, long long lane_bytes, LevelGeom L, int P)
+                                                     uint8_t* __restrict__ pyr, long long lane_bytes, LevelGeom L, int P,
+                                                     int c_begin, int c_end)
 {
-    const int q = blockIdx.x * blockDim.x + threadIdx.x;
-    const int px = q * 4 - P;
-    if (px >= L.w + P) return;
+    const int c = c_begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= c_end) return;
+    const int x0 = 16 * c - P;
     const int py = (int)blockIdx.y - P;
     const int lane = blockIdx.z;
-    const int sy = reflect101(py, L.h);
-    const uint8_t* srow = raw + (size_t)lane * raw_lane + (size_t)sy * raw_pitch;
-    uint32_t v;
-    if (px >= 4 && px + 7 < L.w) {
-        // two aligned words + funnel shift: rows of any pitch / alignment (compact uploads have pitch = width); the eight
-        // bytes read lie inside this row
-        const uintptr_t addr = reinterpret_cast<uintptr_t>(srow + px);
-        const uint32_t* wp = reinterpret_cast<const uint32_t*>(addr & ~(uintptr_t)3);
-        v = __funnelshift_r(__ldg(wp), __ldg(wp + 1), 8 * (int)(addr & 3));
-    } else {
-        v = 0;
+    const uint8_t* srow = raw + (size_t)lane * raw_lane + (size_t)reflect101(py, L.h) * raw_pitch;
+    const uintptr_t addr = reinterpret_cast<uintptr_t>(srow + x0);
+    const uint32_t* wp = reinterpret_cast<const uint32_t*>(addr & ~(uintptr_t)3);
+    const int sh = 8 * (int)(addr & 3);
+    const uint32_t w0 = __ldg(wp), w1 = __ldg(wp + 1), w2 = __ldg(wp + 2), w3 = __ldg(wp + 3), w4 = __ldg(wp + 4);
+    uint4 v;
+    v.x = __funnelshift_r(w0, w1, sh);
+    v.y = __funnelshift_r(w1, w2, sh);
+    v.z = __funnelshift_r(w2, w3, sh);
+    v.w = __funnelshift_r(w3, w4, sh);
+    uint8_t* drow = pyr + (size_t)lane * lane_bytes + L.off + (long long)py * L.pitch;
+    *reinterpret_cast<uint4*>(drow + x0) = v;
+}
+
+__global__ void __launch_bounds__(128) ingest_edge_kernel(const uint8_t* __restrict__ raw, size_t raw_pitch, size_t raw_lane,
+                                                          uint8_t* __restrict__ pyr, long long lane_bytes, LevelGeom L, int P,
+                                                          int c_begin, int c_end, int n_chunks)
+{
+    const int row = blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= L.h + 2 * P) return;
+    // edge chunk e: the chunks before c_begin, then those from c_end on
+    const int e = blockIdx.y;
+    const int c = e < c_begin ? e : c_end + (e - c_begin);
+    if (c >= n_chunks) return;
+    const int x0 = 16 * c - P;
+    const int py = row - P;
+    const int lane = blockIdx.z;
+    const uint8_t* srow = raw + (size_t)lane * raw_lane + (size_t)reflect101(py, L.h) * raw_pitch;
+    uint32_t v[4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) v |= (uint32_t)__ldg(srow + reflect101(px + i, L.w)) << (8 * i);
+    for (int q = 0; q < 4; ++q) {
+        v[q] = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) v[q] |= (uint32_t)__ldg(srow + reflect101(x0 + 4 * q + i, L.w)) << (8 * i);
     }
     uint8_t* drow = pyr + (size_t)lane * lane_bytes + L.off + (long long)py * L.pitch;
-    *reinterpret_cast<uint32_t*>(drow + px) = v;
+    *reinterpret_cast<uint4*>(drow + x0) = make_uint4(v[0], v[1], v[2], v[3]);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -98,30 +126,42 @@ __global__ void __launch_bounds__(128) pyrdown_kernel(uint8_t* __restrict__ pyr,
     uint8_t* lv = base + D.off;
     // does any pixel of the quad have mirror images among the margin columns?  (x <= P on the left, x >= w-1-P on the right)
     const bool colwork = px <= P || px + nv - 1 >= D.w - 1 - P;
-    const int perh = 2 * D.h - 2, perw = 2 * D.w - 2;   // periods of the reflection (levels are larger than 1 x 1)
-    // all rows t in [-P, h+P) with reflect101(t) == py: t = +-py + k perh
-#pragma unroll 1
-    for (int sgn = 0; sgn < 2; ++sgn) {
-        if (sgn == 1 && (py == 0 || py == D.h - 1)) break;          // -py is the same residue as py
-        int t = sgn ? -py : py;
-        t = first_at_least(t, perh, -P);
-#pragma unroll 1
-        for (; t < D.h + P; t += perh) {
+    if (P <= D.w - 1 && P <= D.h - 1) {
+        // the usual case: the margin is narrower than the level, every pixel has at most one mirror image per side
+        auto put_row = [&](int t) {
             uint8_t* drow = lv + (long long)t * D.pitch;
             if (nv == 4) *reinterpret_cast<uint32_t*>(drow + px) = out;
             else
                 for (int i = 0; i < nv; ++i) drow[px + i] = (uint8_t)(out >> (8 * i));
             if (colwork) {
-                for (int i = 0; i < nv; ++i) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
                     const int x = px + i;
                     const uint8_t v = (uint8_t)(out >> (8 * i));
-                    for (int sg = 0; sg < 2; ++sg) {
-                        if (sg == 1 && (x == 0 || x == D.w - 1)) break;
-                        int c = sg ? -x : x;
-                        c = first_at_least(c, perw, -P);
-                        for (; c < D.w + P; c += perw)
-                            if (c != x) drow[c] = v;
-                    }
+                    if (x >= 1 && x <= P) drow[-x] = v;
+                    if (x >= D.w - 1 - P && x <= D.w - 2) drow[2 * (D.w - 1) - x] = v;
+                }
+            }
+        };
+        put_row(py);
+        if (py >= 1 && py <= P) put_row(-py);
+        if (py >= D.h - 1 - P && py <= D.h - 2) put_row(2 * (D.h - 1) - py);
+        return;
+    }
+    // tiny levels: all rows t in [-P, h+P) with reflect101(t) == py are t = +-py + k (2h - 2); the same for columns
+    const int perh = 2 * D.h - 2, perw = 2 * D.w - 2;
+#pragma unroll 1
+    for (int sgn = 0; sgn < 2; ++sgn) {
+        if (sgn == 1 && (py == 0 || py == D.h - 1)) break;          // -py is the same residue as py
+#pragma unroll 1
+        for (int t = first_at_least(sgn ? -py : py, perh, -P); t < D.h + P; t += perh) {
+            uint8_t* drow = lv + (long long)t * D.pitch;
+            for (int i = 0; i < nv; ++i) {
+                const int x = px + i;
+                const uint8_t v = (uint8_t)(out >> (8 * i));
+                for (int sg = 0; sg < 2; ++sg) {
+                    if (sg == 1 && (x == 0 || x == D.w - 1)) break;
+                    for (int c = first_at_least(sg ? -x : x, perw, -P); c < D.w + P; c += perw) drow[c] = v;
                 }
             }
         }
@@ -132,9 +172,20 @@ void launch_ingest(cudaStream_t st, const uint8_t* raw, size_t raw_pitch, size_t
                    const PyrGeom& g, int batch, long long* launches)
 {
     const LevelGeom& L = g.lv[0];
-    const int quads = (L.w + 2 * g.P + 3) / 4;
-    dim3 grid((quads + 127) / 128, L.h + 2 * g.P, batch);
-    ingest_kernel<<<grid, 128, 0, st>>>(raw, raw_pitch, raw_lane, pyr, g.lane_bytes, L, g.P);
+    const int P = g.P;                                        // a multiple of 16
+    const int n_chunks = (L.w + 2 * P + 15) / 16;             // the row pitch (a multiple of 128) covers the last chunk
+    // streaming chunks: x0 = 16 c - P >= 0 and x0 + 20 <= w
+    const int c_begin = P / 16;
+    const int c_end = L.w >= 20 ? std::max(c_begin, (L.w - 20 + P) / 16 + 1) : c_begin;
+    const int rows = L.h + 2 * P;
+    if (c_end > c_begin) {
+        dim3 grid((c_end - c_begin + 127) / 128, rows, batch);
+        ingest_kernel<<<grid, 128, 0, st>>>(raw, raw_pitch, raw_lane, pyr, g.lane_bytes, L, P, c_begin, c_end);
+        if (launches) ++*launches;
+    }
+    const int n_edge = c_begin + (n_chunks - c_end);
+    dim3 egrid((rows + 127) / 128, n_edge, batch);
+    ingest_edge_kernel<<<egrid, 128, 0, st>>>(raw, raw_pitch, raw_lane, pyr, g.lane_bytes, L, P, c_begin, c_end, n_chunks);
     if (launches) ++*launches;
 }
 
