@@ -81,6 +81,8 @@ struct svo_gpu_ctx {
     // frame ingest pipelining: the next step's host frames are copied on a second stream while this step computes
     cudaStream_t copy_st = nullptr;
     cudaEvent_t ev_copy = nullptr;
+    cudaStream_t out_st = nullptr;     // LK results go back to the host on this stream while FAST and bucketing still run
+    cudaEvent_t ev_klt = nullptr, ev_out = nullptr;
     const uint8_t* pf_ptr = nullptr;   // host pointer of the prefetched frames (nullptr = none pending)
     int pf_slot = -1;
     float stage_ms[4] = {0, 0, 0, 0};
@@ -239,6 +241,9 @@ static int create_buffers(svo_gpu_ctx* ctx)
     for (auto& e : ctx->ev) CK(cudaEventCreate(&e));
     CK(cudaStreamCreateWithFlags(&ctx->copy_st, cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&ctx->ev_copy, cudaEventDisableTiming));
+    CK(cudaStreamCreateWithFlags(&ctx->out_st, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&ctx->ev_klt, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&ctx->ev_out, cudaEventDisableTiming));
     CK(cudaStreamSynchronize(ctx->st));
     return 0;
 }
@@ -287,6 +292,9 @@ extern "C" int svo_gpu_destroy(svo_gpu_ctx* ctx)
     if (ctx->st) cudaStreamSynchronize(ctx->st);
     if (ctx->copy_st) { cudaStreamSynchronize(ctx->copy_st); cudaStreamDestroy(ctx->copy_st); }
     if (ctx->ev_copy) cudaEventDestroy(ctx->ev_copy);
+    if (ctx->out_st) { cudaStreamSynchronize(ctx->out_st); cudaStreamDestroy(ctx->out_st); }
+    if (ctx->ev_klt) cudaEventDestroy(ctx->ev_klt);
+    if (ctx->ev_out) cudaEventDestroy(ctx->ev_out);
     for (auto& s : ctx->slots) {
         cudaFree(s.raw_own.p);
         cudaFree(s.pyr.p);
