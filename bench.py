@@ -213,6 +213,10 @@ def run_b200(args):
         raise SystemExit("bench.py: no CUDA device; the front-end has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     if world > 1:
+        # stdout carries exactly one JSON line: NCCL's version banner (NCCL_DEBUG=VERSION on some boxes) goes to stderr
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", "WARN"):
+            os.environ.pop("NCCL_DEBUG")
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     wl = synth.WORKLOADS[args.workload]
     w, h, S, K, W = wl["w"], wl["h"], args.streams, args.steps, args.warmup
