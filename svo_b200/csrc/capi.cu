@@ -225,7 +225,7 @@ static int create_buffers(svo_gpu_ctx* ctx)
     if (int r = dmalloc(ctx, ctx->trk_err, B * NP)) return r;
     if (int r = dmalloc(ctx, ctx->trk_n, B)) return r;
     if (int r = dmalloc(ctx, ctx->int_max, B)) return r;
-    if (int r = dmalloc(ctx, ctx->d_iters, 1)) return r;
+    if (int r = dmalloc(ctx, ctx->d_iters, 2)) return r;   // [0] LK iterations, [1] LK work counter
     if (int r = dmalloc(ctx, ctx->flt_index, B * NP)) return r;
     if (int r = dmalloc(ctx, ctx->flt_a, B * NP)) return r;
     if (int r = dmalloc(ctx, ctx->flt_b, B * NP)) return r;

@@ -24,6 +24,7 @@
 //     loads and forms Ix, Iy separably.  Windows that touch the image border (where OpenCV's derivative image is
 //     ZERO-padded, which breaks that identity) take the literal path: Scharr plane with zeros outside, then bilinear.
 //   - lanes never diverge: every per-feature scalar is warp-uniform; reductions are REDUX on 16-bit halves (exact).
+#include <algorithm>
 #include <type_traits>
 
 #include "klt_common.cuh"
@@ -197,10 +198,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) klt_run_kernel(const KltArgs
     __shared__ __align__(16) uint32_t smem[WARPS * G::WARP_WORDS];
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int lane_id = blockIdx.y;
-    const int n = min(a.n_dev[lane_id], a.n_max);
-    const int pt = blockIdx.x * WARPS + warp;
-    if (pt >= n) return;
+    static_assert(WARPS == 1, "a CTA is one warp: it fetches one track at a time");
 
     uint32_t* region = smem + warp * G::WARP_WORDS;
     int* plane = reinterpret_cast<int*>(region + G::REGION_WORDS);
@@ -231,13 +229,25 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) klt_run_kernel(const KltArgs
 
     int Iw[RPL][8], Gx[RPL][8 * NG];   // Gx: Ix then Iy (NG == 2) or (Ix & 0xffff) | (Iy << 16) (PACKG)
 
+    const float halfx = (WW - 1) * 0.5f, halfy = (WH - 1) * 0.5f;
+    const float FLT_SCALE = 1.f / (1 << 20);
+    // Persistent CTAs (one warp each, as many as fit on the device): tracks are handed out one at a time through a global
+    // counter, so a CTA that finishes a short track fetches the next one at once (tracks differ a lot in iteration count)
+    // and the per-lane constants above are set up once per CTA instead of once per track.
+    const unsigned total = (unsigned)a.n_max * gridDim.y;   // gridDim.y carries the batch
+    unsigned long long iters_cta = 0;
+    for (;;) {
+    unsigned t = 0;
+    if (lane == 0) t = atomicAdd(a.work, 1u);
+    t = __shfl_sync(kFull, t, 0);
+    if (t >= total) break;
+    const int lane_id = (int)(t / (unsigned)a.n_max), pt = (int)(t - (unsigned)lane_id * (unsigned)a.n_max);
+    if (pt >= min(a.n_dev[lane_id], a.n_max)) continue;
     const size_t pbase = (size_t)lane_id * a.pts_lane + pt;
     const float2 prev = a.prev_xy[pbase];
     const uint8_t* Ppyr = a.prev_pyr + (size_t)lane_id * a.g.lane_bytes;
     const uint8_t* Npyr = a.next_pyr + (size_t)lane_id * a.g.lane_bytes;
 
-    const float halfx = (WW - 1) * 0.5f, halfy = (WH - 1) * 0.5f;
-    const float FLT_SCALE = 1.f / (1 << 20);
     float ox = 0.f, oy = 0.f;   // nextPts[pt]
     int st = 1;
     float er = 0.f;
@@ -550,14 +560,27 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) klt_run_kernel(const KltArgs
         a.next_xy[pbase] = make_float2(ox, oy);
         a.status[pbase] = (uint8_t)st;
         a.err[pbase] = er;
-        if (a.iters) atomicAdd(a.iters, (unsigned long long)iters);
     }
+    iters_cta += iters;
+    cp_async_wait_all();
+    __syncwarp();
+    }   // next track
+    if (lane == 0 && a.iters) atomicAdd(a.iters, iters_cta);
 }
 
 template <int WW, int WH, int WARPS, bool PACKG, int MINB>
 void launch_run(cudaStream_t st, const KltArgs& a, int batch)
 {
-    dim3 grid((a.n_max + WARPS - 1) / WARPS, batch);
+    static int sms = 0;
+    if (!sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    const long long total = (long long)a.n_max * batch;
+    dim3 grid((unsigned)std::min<long long>(total, (long long)sms * MINB), batch);
+    grid.x = (grid.x + batch - 1) / batch;   // gridDim.y = batch only tells the kernel the batch size
+    cudaMemsetAsync(a.work, 0, sizeof(unsigned), st);
     klt_run_kernel<WW, WH, WARPS, PACKG, MINB><<<grid, WARPS * 32, 0, st>>>(a);
 }
 

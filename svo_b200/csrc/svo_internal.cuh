@@ -109,6 +109,7 @@ struct KltArgs {
     int flags;
     double min_eig_threshold;
     unsigned long long* iters; // optional global iteration counter
+    unsigned* work;            // track hand-out counter of the persistent variant (zeroed by the launcher)
 };
 void launch_klt(cudaStream_t st, const KltArgs& a, int batch, long long* launches);
 
