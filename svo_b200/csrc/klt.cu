@@ -29,11 +29,25 @@
 
 #include "klt_common.cuh"
 
+// epilogue shortcuts of the Newton loop, individually switchable for the variant sweeps (scripts/build_variants.sh):
+//   1 scaled warp sum (one FMA instead of add + multiply)      2 float pre-test in front of the double convergence test
+//   4 weight pairs packed by PRMT                               8 level-bounds test only when the window leaves the staged region
+// Measured (gpurun_out/s5): 1 and 4 each save ~1 %, 2 and 8 are slower (extra branch / registers) and stay off.
+#ifndef KLT_OPTS
+#define KLT_OPTS 5
+#endif
+
 namespace svo {
 
 namespace {
 
 using namespace lk;
+
+__device__ __forceinline__ float warp_sum_scaled(int v)
+{
+    if constexpr (KLT_OPTS & 1) return warp_sum_exact_scaled(v);
+    else return __fmul_rn(warp_sum_exact_f(v), 1.f / (1 << 20));
+}
 
 template <int WW, int WH>
 struct RunGeo {
@@ -156,7 +170,11 @@ __device__ __forceinline__ int dp2a_hi_su(uint32_t a, uint32_t b, int c)
     asm("dp2a.hi.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
     return d;
 }
-__device__ __forceinline__ uint32_t pack_weights(int lo, int hi) { return ((uint32_t)lo & 0xffffu) | ((uint32_t)hi << 16); }
+__device__ __forceinline__ uint32_t pack_weights(int lo, int hi)
+{
+    if constexpr (KLT_OPTS & 4) return __byte_perm((uint32_t)lo, (uint32_t)hi, 0x5410);
+    else return ((uint32_t)lo & 0xffffu) | ((uint32_t)hi << 16);
+}
 
 template <int I>
 __device__ __forceinline__ int run_px(const RunRow& top, const RunRow& bot, uint32_t wt, uint32_t wb, int c)
@@ -230,7 +248,8 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) klt_run_kernel(const KltArgs
     int Iw[RPL][8], Gx[RPL][8 * NG];   // Gx: Ix then Iy (NG == 2) or (Ix & 0xffff) | (Iy << 16) (PACKG)
 
     const float halfx = (WW - 1) * 0.5f, halfy = (WH - 1) * 0.5f;
-    const float FLT_SCALE = 1.f / (1 << 20);
+    // float brackets of eps^2 for the convergence test: a float sum of squares outside [eps_lo, eps_hi] decides the double test
+    const float eps_lo = __double2float_rd(a.eps2 * 0.99999), eps_hi = __double2float_ru(a.eps2 * 1.00001);
     // Persistent CTAs (one warp each, as many as fit on the device): tracks are handed out one at a time through a global
     // counter, so a CTA that finishes a short track fetches the next one at once (tracks differ a lot in iteration count)
     // and the per-lane constants above are set up once per CTA instead of once per track.
@@ -284,6 +303,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) klt_run_kernel(const KltArgs
         const uint8_t* Jorigin = Npyr + L.off;
         int sx0 = 0, sy0 = 0;      // image coordinates of region byte (0, 0)
         bool jstaged = false;
+        bool rsafe = false;        // staged, and every window origin inside the region passes the level-bounds test
         auto stage_j = [&](int inx, int iny) {
             sx0 = (inx - G::MJ) & ~3;
             sy0 = iny - G::MJ;
@@ -292,6 +312,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) klt_run_kernel(const KltArgs
             for (int k = 0; k < G::PASSJ; ++k)
                 cp_async4(sJ_dst + k * G::RPPJ * G::PJ, src + (long long)(k * G::RPPJ) * L.pitch);
             jstaged = true;
+            rsafe = sx0 >= -WW && sx0 + G::DXMAX < L.w && sy0 >= -WH && sy0 + G::DYMAX < L.h;
         };
         cp_async_wait_all();   // a copy started at a level that was then skipped may still be in flight
         __syncwarp();          // and every lane is done reading the previous level's regions
@@ -458,9 +479,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) klt_run_kernel(const KltArgs
                 }
             }
         }
-        const float A11 = __fmul_rn(warp_sum_exact_f(sA11), FLT_SCALE);
-        const float A12 = __fmul_rn(warp_sum_exact_f(sA12), FLT_SCALE);
-        const float A22 = __fmul_rn(warp_sum_exact_f(sA22), FLT_SCALE);
+        const float A11 = warp_sum_scaled(sA11), A12 = warp_sum_scaled(sA12), A22 = warp_sum_scaled(sA22);   // x FLT_SCALE
 
         float D = __fsub_rn(__fmul_rn(A11, A22), __fmul_rn(A12, A12));
         const float minEig = min_eig(A11, A12, A22, WW * WH);
@@ -515,22 +534,32 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) klt_run_kernel(const KltArgs
         float pdx = 0.f, pdy = 0.f;
         for (int j = 0; j < a.max_count; ++j) {
             const int inx = (int)floorf(nx), iny = (int)floorf(ny);
-            if (inx < -WW || inx >= L.w || iny < -WH || iny >= L.h) {
-                if (level == 0) st = 0;
-                break;
+            int wdx = inx - sx0, wdy = iny - sy0, sb1, sb2;
+            if (!(KLT_OPTS & 8) || !rsafe || (unsigned)wdx > (unsigned)G::DXMAX || (unsigned)wdy > (unsigned)G::DYMAX) {
+                if (inx < -WW || inx >= L.w || iny < -WH || iny >= L.h) {
+                    if (level == 0) st = 0;
+                    break;
+                }
+                locate(inx, iny, wdx, wdy);
             }
             ++iters;
             w = bilinear_weights(__fsub_rn(nx, (float)inx), __fsub_rn(ny, (float)iny));
-            int wdx, wdy, sb1, sb2;
-            locate(inx, iny, wdx, wdy);
             window_pass(wdx, wdy, sb1, sb2, std::false_type{});
-            const float b1 = __fmul_rn(warp_sum_exact_f(sb1), FLT_SCALE);
-            const float b2 = __fmul_rn(warp_sum_exact_f(sb2), FLT_SCALE);
+            const float b1 = warp_sum_scaled(sb1), b2 = warp_sum_scaled(sb2);   // x FLT_SCALE
             const float dx = __fmul_rn(__fsub_rn(__fmul_rn(A12, b2), __fmul_rn(A22, b1)), D);
             const float dy = __fmul_rn(__fsub_rn(__fmul_rn(A12, b1), __fmul_rn(A11, b2)), D);
             nx = __fadd_rn(nx, dx); ny = __fadd_rn(ny, dy);
             ox = __fadd_rn(nx, halfx); oy = __fadd_rn(ny, halfy);
-            if (__dadd_rn(__dmul_rn((double)dx, (double)dx), __dmul_rn((double)dy, (double)dy)) <= a.eps2) break;
+            // OpenCV tests delta.ddot(delta) <= eps^2 in double.  The float sum of squares is within 2e-7 of it, so outside the
+            // bracket (1 -+ 1e-5) eps^2 it decides the test; NaNs and the bracket itself take the double path.
+            if constexpr (KLT_OPTS & 2) {
+                const float ss = __fmaf_rn(dx, dx, __fmul_rn(dy, dy));
+                if (ss < eps_lo) break;
+                if (!(ss > eps_hi) &&
+                    __dadd_rn(__dmul_rn((double)dx, (double)dx), __dmul_rn((double)dy, (double)dy)) <= a.eps2) break;
+            } else {
+                if (__dadd_rn(__dmul_rn((double)dx, (double)dx), __dmul_rn((double)dy, (double)dy)) <= a.eps2) break;
+            }
             // |d + dprev| < 0.01 (a double in OpenCV): 0.01f is the largest float below 0.01, so the float test `<= 0.01f` is the same
             if (j > 0 && fabsf(__fadd_rn(dx, pdx)) <= 0.01f && fabsf(__fadd_rn(dy, pdy)) <= 0.01f) {
                 ox = __fsub_rn(ox, __fmul_rn(dx, 0.5f));

@@ -45,6 +45,15 @@ __device__ __forceinline__ float warp_sum_exact_f(int v)
     return __fadd_rn(__fmul_rn(__int2float_rn(hi), 65536.f), __uint2float_rn(lo));
 }
 
+// FLT_SCALE (2^-20) times that sum, one instruction shorter: hi 2^-4 and lo 2^-20 are exact, so the FMA rounds once, at the
+// same place as the addition above (scaling by a power of two commutes with round-to-nearest; no underflow, |sum| >= 1 or 0)
+__device__ __forceinline__ float warp_sum_exact_scaled(int v)
+{
+    const unsigned lo = __reduce_add_sync(kFull, (unsigned)(v & 0xffff));
+    const int hi = __reduce_add_sync(kFull, v >> 16);
+    return __fmaf_rn(__uint2float_rn(lo), 1.f / (1 << 20), __fmul_rn(__int2float_rn(hi), 1.f / 16.f));
+}
+
 // unrounded bilinear sample at byte pointer p (row pitch rp)
 __device__ __forceinline__ int bilin(const uint8_t* __restrict__ p, int rp, const BiW& w)
 {
