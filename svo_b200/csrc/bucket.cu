@@ -143,6 +143,8 @@ void launch_bucket(cudaStream_t st, const float2* in_xy, const int* in_age, size
     cudaMemsetAsync(bb.err_flag, 0, sizeof(int) * batch, st);
     int nblk = (n_max + 255) / 256;
     nblk = nblk < 1 ? 1 : (nblk > 592 ? 592 : nblk);   // 148 SMs x 4
+    static bool once = false;
+    if (!once) { prefer_max_shared(bucket_insert_kernel); prefer_max_shared(bucket_emit_kernel); once = true; }
     bucket_insert_kernel<<<dim3(nblk, batch), 256, 0, st>>>(in_xy, in_lane, n_dev, n_max, Wc, nb, bucket_size, k, bb);
     bucket_emit_kernel<<<dim3((nb + 255) / 256, batch), 256, 0, st>>>(in_xy, in_age, in_lane, Wc, nb, k, bb);
     if (launches) *launches += 2;

@@ -3,6 +3,7 @@
 #include <limits.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -83,6 +84,14 @@ struct svo_gpu_ctx {
     cudaEvent_t ev_copy = nullptr;
     cudaStream_t out_st = nullptr;     // LK results go back to the host on this stream while FAST and bucketing still run
     cudaEvent_t ev_klt = nullptr, ev_out = nullptr;
+    // detection beside tracking: mask, FAST and bucketing run on aux_st while the LK kernel keeps klt_reserve CTA slots per
+    // SM free for them; a helper launch of the LK kernel on aux_st takes those slots over afterwards (same work queue)
+    cudaStream_t aux_st = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    cudaEvent_t eva[4] = {nullptr, nullptr, nullptr, nullptr};
+    int overlap = 0;        // SVO_GPU_STEP_OVERLAP (0 = one stream, stages back to back; 1 measured slower, gpurun_out/s6)
+    int klt_reserve = 3;    // SVO_GPU_KLT_RESERVE
+    int fast_small = 1;     // SVO_GPU_FAST_SMALL: 128-thread FAST CTAs in the overlapped step
     const uint8_t* pf_ptr = nullptr;   // host pointer of the prefetched frames (nullptr = none pending)
     int pf_slot = -1;
     float stage_ms[4] = {0, 0, 0, 0};
@@ -244,6 +253,13 @@ static int create_buffers(svo_gpu_ctx* ctx)
     CK(cudaStreamCreateWithFlags(&ctx->out_st, cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&ctx->ev_klt, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&ctx->ev_out, cudaEventDisableTiming));
+    CK(cudaStreamCreateWithFlags(&ctx->aux_st, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
+    for (auto& e : ctx->eva) CK(cudaEventCreate(&e));
+    if (const char* v = getenv("SVO_GPU_STEP_OVERLAP")) ctx->overlap = atoi(v);
+    if (const char* v = getenv("SVO_GPU_KLT_RESERVE")) ctx->klt_reserve = atoi(v);
+    if (const char* v = getenv("SVO_GPU_FAST_SMALL")) ctx->fast_small = atoi(v);
     CK(cudaStreamSynchronize(ctx->st));
     return 0;
 }
@@ -295,6 +311,10 @@ extern "C" int svo_gpu_destroy(svo_gpu_ctx* ctx)
     if (ctx->out_st) { cudaStreamSynchronize(ctx->out_st); cudaStreamDestroy(ctx->out_st); }
     if (ctx->ev_klt) cudaEventDestroy(ctx->ev_klt);
     if (ctx->ev_out) cudaEventDestroy(ctx->ev_out);
+    if (ctx->aux_st) { cudaStreamSynchronize(ctx->aux_st); cudaStreamDestroy(ctx->aux_st); }
+    if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+    if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
+    for (auto& e : ctx->eva) if (e) cudaEventDestroy(e);
     for (auto& s : ctx->slots) {
         cudaFree(s.raw_own.p);
         cudaFree(s.pyr.p);

@@ -83,9 +83,11 @@ __device__ __forceinline__ uint32_t packed_best(const uint32_t (&D)[16])
 
 // scalar cornerScore<16> kept for reference in comments of the tests: see oracle/svo_oracle.c:orc_corner_score
 
-__global__ void __launch_bounds__(256) fast_tile_kernel(const uint8_t* __restrict__ raw, size_t raw_pitch, size_t raw_lane,
-                                                        int w, int h, int t, int nms, const uint8_t* __restrict__ mask,
-                                                        size_t mask_pitch, size_t mask_lane, FastBufs fb, int ntx)
+// NT threads per CTA (256, or 128 when the CTAs are meant to fit beside the persistent LK kernel: 8 192 registers each)
+template <int NT>
+__global__ void __launch_bounds__(NT) fast_tile_kernel(const uint8_t* __restrict__ raw, size_t raw_pitch, size_t raw_lane,
+                                                       int w, int h, int t, int nms, const uint8_t* __restrict__ mask,
+                                                       size_t mask_pitch, size_t mask_lane, FastBufs fb, int ntx)
 {
     __shared__ __align__(16) uint32_t simg_pad[RH * RWW + 2];   // one pad word on each side: ring_word reads words g-1, g+1
     __shared__ __align__(16) uint32_t sbest_pad[SH * RWW + 2];  // excess of the score over the threshold, one byte per pixel,
@@ -101,7 +103,7 @@ __global__ void __launch_bounds__(256) fast_tile_kernel(const uint8_t* __restric
 
     // ---- stage the (TW+8) x (TH+8) region; coordinates are clamped to the image (clamped pixels are never used by a
     //      valid candidate: those sit at least 3 px inside the image)
-    for (int i = tid; i < RH * RWW; i += 256) {
+    for (int i = tid; i < RH * RWW; i += NT) {
         const int r = i / RWW, cw = i - r * RWW;
         const int gy = min(max(y0 - 4 + r, 0), h - 1);
         const int gx = x0 - 4 + cw * 4;
@@ -125,7 +127,7 @@ __global__ void __launch_bounds__(256) fast_tile_kernel(const uint8_t* __restric
     //      columns 0 .. RW-1): sbest byte = max(best - t, 0), where best = cornerScore + 1.
     const uint32_t bias = 0x01000100u;
     const uint32_t tt = (uint32_t)t * 0x00010001u;
-    for (int idx = tid; idx < SH * NG; idx += 256) {
+    for (int idx = tid; idx < SH * NG; idx += NT) {
         const int r = idx / NG, g = idx - r * NG;
         const uint32_t* c = simg + (r + 3) * RWW + g;   // centre row of score row r
         const uint32_t wc = c[0];
@@ -178,7 +180,7 @@ __global__ void __launch_bounds__(256) fast_tile_kernel(const uint8_t* __restric
     const uint32_t lt = (1u << ln) - 1u;
     // OpenCV compares scores (= best - 1); a corner of score 0 (threshold 0 only) never beats a non-corner's 0
     const uint32_t nms_floor = (nms && t == 0) ? 0x00010001u : 0u;
-    for (int r = warp; r < TH; r += 8) {
+    for (int r = warp; r < TH; r += NT / 32) {
         const int gy = y0 + r;
         if (gy >= h) break;   // warp-uniform
         const uint32_t* b = sbest + (r + 1) * RWW + ln + 1;   // tile pixel x = 4 ln + i sits in staged group ln + 1
@@ -301,7 +303,7 @@ __global__ void __launch_bounds__(128) mask_boxes_kernel(uint8_t* __restrict__ m
 
 void launch_fast(cudaStream_t st, const uint8_t* raw, size_t raw_pitch, size_t raw_lane, int w, int h, int threshold,
                  int nms, const uint8_t* mask, size_t mask_pitch, size_t mask_lane, const FastBufs& fb, int batch,
-                 long long* launches)
+                 long long* launches, bool small_ctas)
 {
     threshold = threshold < 0 ? 0 : (threshold > 255 ? 255 : threshold);
     cudaMemsetAsync(fb.rowtotal, 0, sizeof(int) * (size_t)fb.rows_cap * batch, st);
@@ -309,10 +311,19 @@ void launch_fast(cudaStream_t st, const uint8_t* raw, size_t raw_pitch, size_t r
         cudaMemsetAsync(fb.kp_count, 0, sizeof(int) * batch, st);
         return;
     }
+    static bool once = false;
+    if (!once) {
+        prefer_max_shared(fast_tile_kernel<128>); prefer_max_shared(fast_tile_kernel<256>); prefer_max_shared(fast_gather_kernel);
+        once = true;
+    }
     const int ntx = (w + TW - 1) / TW;
     dim3 grid(ntx, (h + TH - 1) / TH, batch);
-    fast_tile_kernel<<<grid, 256, 0, st>>>(raw, raw_pitch, raw_lane, w, h, threshold, nms, mask, mask_pitch, mask_lane,
-                                           fb, ntx);
+    if (small_ctas)
+        fast_tile_kernel<128><<<grid, 128, 0, st>>>(raw, raw_pitch, raw_lane, w, h, threshold, nms, mask, mask_pitch, mask_lane,
+                                                    fb, ntx);
+    else
+        fast_tile_kernel<256><<<grid, 256, 0, st>>>(raw, raw_pitch, raw_lane, w, h, threshold, nms, mask, mask_pitch, mask_lane,
+                                                    fb, ntx);
     fast_gather_kernel<<<dim3(h, batch), 128, 0, st>>>(w, h, threshold, nms, fb, ntx);
     if (launches) *launches += 2;
 }
@@ -324,6 +335,8 @@ void launch_build_mask(cudaStream_t st, uint8_t* mask, size_t mask_pitch, size_t
     // one fill for all lanes (lanes are mask_lane apart and the padding of a lane is never read)
     cudaMemsetAsync(mask, 255, (size_t)(batch - 1) * mask_lane + (size_t)(h - 1) * mask_pitch + (size_t)w, st);
     if (n_max <= 0) return;
+    static bool once = false;
+    if (!once) { prefer_max_shared(mask_boxes_kernel); once = true; }
     mask_boxes_kernel<<<dim3((n_max + 3) / 4, batch), 128, 0, st>>>(mask, mask_pitch, mask_lane, w, h, pts, pts_lane,
                                                                   n_dev, n_max, half);
     if (launches) ++*launches;

@@ -29,6 +29,14 @@ struct PyrGeom {
     long long lane_bytes;   // stride between lanes
 };
 
+// Kernels that may share an SM with the persistent LK kernel (the step runs FAST and bucketing beside it) all ask for
+// the same, largest shared-memory carve-out: CTAs of kernels with different carve-outs cannot be co-resident on an SM.
+template <class Kernel>
+inline void prefer_max_shared(Kernel k)
+{
+    cudaFuncSetAttribute(k, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+}
+
 // REFLECT_101 index map (cv::BORDER_REFLECT_101), valid for any i when n >= 2 (loops for tiny n), n == 1 -> 0
 __host__ __device__ inline int reflect101(int i, int n)
 {
@@ -63,7 +71,7 @@ struct FastBufs {
 // mask: device u8 plane per lane (pitch mask_pitch, lane stride mask_lane) or nullptr
 void launch_fast(cudaStream_t st, const uint8_t* raw, size_t raw_pitch, size_t raw_lane, int w, int h, int threshold,
                  int nms, const uint8_t* mask, size_t mask_pitch, size_t mask_lane, const FastBufs& fb, int batch,
-                 long long* launches);
+                 long long* launches, bool small_ctas = false);
 // mask plane = 255, then 0 in the rounded inclusive box around each point (src/tracking.cpp:76-79)
 // pts: [B][pts_lane] float2, n per lane from n_dev[lane] (device) clamped to n_max
 void launch_build_mask(cudaStream_t st, uint8_t* mask, size_t mask_pitch, size_t mask_lane, int w, int h,
@@ -111,7 +119,10 @@ struct KltArgs {
     unsigned long long* iters; // optional global iteration counter
     unsigned* work;            // track hand-out counter of the persistent variant (zeroed by the launcher)
 };
-void launch_klt(cudaStream_t st, const KltArgs& a, int batch, long long* launches);
+// part / reserve: see klt.cu:launch_run.  kKltMain and kKltHelper expect klt_zero_work() to have run first (stream-ordered).
+enum KltPart { kKltAll = 0, kKltMain = 1, kKltHelper = 2 };
+void klt_zero_work(cudaStream_t st, const KltArgs& a);
+void launch_klt(cudaStream_t st, const KltArgs& a, int batch, long long* launches, int part = kKltAll, int reserve = 0);
 
 // ------------------------------------------------------------------------------------------------ filter.cu
 struct FilterArgs {
