@@ -80,6 +80,17 @@ SVO_GPU_API int svo_gpu_upload(svo_gpu_ctx* ctx, int slot, const uint8_t* host, 
 SVO_GPU_API int svo_gpu_upload_batch(svo_gpu_ctx* ctx, int slot, const uint8_t* images, int mem_kind, int w, int h,
                                      size_t stride_bytes, size_t image_stride_bytes, int batch);
 
+/* Colour frames: `host` / `images` are interleaved 8-bit BGR (cv::Mat CV_8UC3 as cv::imread returns it; stride_bytes >=
+ * 3 w).  The slot receives cv::cvtColor(img, COLOR_BGR2GRAY) of them, bit for bit (OpenCV 4.x 8-bit fixed point), computed
+ * on the device.  Replaces the host-side conversion of the reference's loader (include/async_image_loader.h:66-69: imread,
+ * then cvtColor when the sequence is the colour one). */
+SVO_GPU_API int svo_gpu_upload_bgr(svo_gpu_ctx* ctx, int slot, const uint8_t* host, int w, int h, size_t stride_bytes);
+SVO_GPU_API int svo_gpu_upload_bgr_batch(svo_gpu_ctx* ctx, int slot, const uint8_t* images, int mem_kind, int w, int h,
+                                         size_t stride_bytes, size_t image_stride_bytes, int batch);
+/* Read-back of the 8-bit gray image lane `lane` of `slot` holds (rows stride_bytes apart): what the reference keeps as
+ * frame->leftImg() / rightImg() (include/frame.h:32-33) when the frame arrived as BGR. */
+SVO_GPU_API int svo_gpu_download_image(svo_gpu_ctx* ctx, int slot, int lane, uint8_t* host, size_t stride_bytes);
+
 /* Builds the Gaussian pyramid of `slot` (all uploaded lanes): level l = pyrDown(level l-1), every level stored with a
  * BORDER_REFLECT_101 margin.  Same result as cv::buildOpticalFlowPyramid(img, pyr, winSize, maxLevel, false), which
  * cv::calcOpticalFlowPyrLK runs on both images on every call (src/tracking.cpp:101-105, :160-165); *levels_out gets the

@@ -30,7 +30,8 @@ _i32p = C.POINTER(C.c_int)
 
 def build(force=False):
     """Compile the C restatement (and oracle/_ref when /root/reference is present)."""
-    if force or not os.path.exists(_LIB) or (os.path.isdir("/root/reference/src") and not os.path.exists(_REF)):
+    stale = os.path.exists(_LIB) and os.path.getmtime(os.path.join(_HERE, "svo_oracle.c")) > os.path.getmtime(_LIB)
+    if force or stale or not os.path.exists(_LIB) or (os.path.isdir("/root/reference/src") and not os.path.exists(_REF)):
         subprocess.check_call(["make", "-C", _HERE, "-s"])
 
 
@@ -51,6 +52,8 @@ def lib():
         _lib.orc_bucket.restype = C.c_int
         _lib.orc_bucket.argtypes = [_f32p, _i32p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _i32p]
         _lib.orc_pyrdown.restype = None
+        _lib.orc_bgr2gray.argtypes = [_u8p, C.c_int, C.c_int, C.c_size_t, _u8p, C.c_size_t]
+        _lib.orc_bgr2gray.restype = None
         _lib.orc_pyrdown.argtypes = [_u8p, C.c_int, C.c_int, C.c_size_t, _u8p, C.c_size_t]
         _lib.orc_scharr.restype = None
         _lib.orc_scharr.argtypes = [_u8p, C.c_int, C.c_int, C.c_size_t, C.POINTER(C.c_int16)]
@@ -137,6 +140,15 @@ def orc_bucket(xy, ages, img_w, img_h, bucket_size, per_bucket):
 def ref_bucket(xy, ages, img_w, img_h, bucket_size, per_bucket):
     """The reference's own FeatureSet::bucketingFeatures (src/bucket.cpp:24-68), compiled unmodified."""
     return _bucket(ref_lib().ref_bucketing, xy, ages, img_w, img_h, bucket_size, per_bucket)
+
+
+def orc_bgr2gray(bgr):
+    """cv::cvtColor(bgr, COLOR_BGR2GRAY) of an (h, w, 3) uint8 image (include/async_image_loader.h:68-69)."""
+    bgr = np.ascontiguousarray(bgr, dtype=np.uint8)
+    h, w, _ = bgr.shape
+    out = np.empty((h, w), np.uint8)
+    lib().orc_bgr2gray(_p(bgr, _u8p), w, h, bgr.strides[0], _p(out, _u8p), out.strides[0])
+    return out
 
 
 def orc_pyrdown(img):

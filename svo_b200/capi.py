@@ -32,6 +32,10 @@ SYMBOLS = {
     "svo_gpu_upload": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_size_t]),
     "svo_gpu_upload_batch": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_size_t,
                                        C.c_size_t, C.c_int]),
+    "svo_gpu_upload_bgr": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_size_t]),
+    "svo_gpu_upload_bgr_batch": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_size_t,
+                                           C.c_size_t, C.c_int]),
+    "svo_gpu_download_image": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_size_t]),
     "svo_gpu_build_pyramid": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, _i32p]),
     "svo_gpu_download_level": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, _i32p, _i32p]),
     "svo_gpu_download_level_padded": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, _i32p, _i32p,
@@ -170,6 +174,28 @@ class Context:
     def upload_batch_device(self, slot, dev_ptr, w, h, stride, image_stride, batch):
         self._ck(self.lib.svo_gpu_upload_batch(self.h, slot, C.c_void_p(dev_ptr), MEM_DEVICE, w, h, stride,
                                                image_stride, batch))
+
+    def upload_bgr(self, slot, img):
+        """(h, w, 3) uint8 BGR image (rows may be strided) -> gray in the slot, cv::cvtColor(COLOR_BGR2GRAY) on the device."""
+        img = np.asarray(img)
+        if img.dtype != np.uint8 or img.ndim != 3 or img.shape[2] != 3 or img.strides[2] != 1 or img.strides[1] != 3:
+            raise ValueError("image must be an (h, w, 3) uint8 array with interleaved channels (CV_8UC3)")
+        self._ck(self.lib.svo_gpu_upload_bgr(self.h, slot, _ptr(img), img.shape[1], img.shape[0], img.strides[0]))
+
+    def upload_bgr_batch(self, slot, imgs):
+        imgs = np.ascontiguousarray(imgs, np.uint8)
+        assert imgs.ndim == 4 and imgs.shape[3] == 3
+        b, h, w, _ = imgs.shape
+        self._ck(self.lib.svo_gpu_upload_bgr_batch(self.h, slot, _ptr(imgs), MEM_HOST, w, h, 3 * w, 3 * w * h, b))
+
+    def upload_bgr_batch_device(self, slot, dev_ptr, w, h, stride, image_stride, batch):
+        self._ck(self.lib.svo_gpu_upload_bgr_batch(self.h, slot, C.c_void_p(dev_ptr), MEM_DEVICE, w, h, stride,
+                                                   image_stride, batch))
+
+    def download_image(self, slot, w, h, lane=0):
+        out = np.empty((h, w), np.uint8)
+        self._ck(self.lib.svo_gpu_download_image(self.h, slot, lane, _ptr(out), out.strides[0]))
+        return out
 
     def build_pyramid(self, slot, win=(21, 21), max_level=3):
         lv = C.c_int(0)

@@ -45,6 +45,8 @@ struct svo_gpu_ctx {
     char err[512] = "";
     long long launches = 0;
 
+    DevBuf bgr_stage;             // device copy of host BGR frames on their way to a slot (svo_gpu_upload_bgr*)
+
     // FAST
     FastBufs fb{};
     DevBuf mask;                  // [B][max_h * mask_pitch]
@@ -320,7 +322,7 @@ extern "C" int svo_gpu_destroy(svo_gpu_ctx* ctx)
         cudaFree(s.pyr.p);
     }
     void* bufs[] = {ctx->fb.rowtotal, ctx->fb.segcnt, ctx->fb.segkp, ctx->fb.kp_xy, ctx->fb.kp_resp, ctx->fb.kp_count,
-                    ctx->mask.p, ctx->bb.out_xy, ctx->bb.out_age, ctx->bb.out_count, ctx->bb.err_flag, ctx->cell_slots.p,
+                    ctx->mask.p, ctx->bgr_stage.p, ctx->bb.out_xy, ctx->bb.out_age, ctx->bb.out_count, ctx->bb.err_flag, ctx->cell_slots.p,
                     ctx->cell_cnt.p, ctx->cell_last.p, ctx->bk_in_xy, ctx->bk_in_age, ctx->trk_xy, ctx->nxt_xy,
                     ctx->trk_status, ctx->trk_err, ctx->trk_n, ctx->int_max, ctx->d_iters, ctx->flt_index, ctx->flt_a,
                     ctx->flt_b, ctx->flt_err, ctx->flt_n};
@@ -391,6 +393,71 @@ extern "C" int svo_gpu_upload_batch(svo_gpu_ctx* ctx, int slot, const uint8_t* i
 extern "C" int svo_gpu_upload(svo_gpu_ctx* ctx, int slot, const uint8_t* host, int w, int h, size_t stride_bytes)
 {
     return svo_gpu_upload_batch(ctx, slot, host, SVO_GPU_MEM_HOST, w, h, stride_bytes, stride_bytes * (size_t)(h > 0 ? h : 0), 1);
+}
+
+// Colour frames: interleaved BGR (cv::Mat CV_8UC3 as cv::imread returns it) -> gray in the slot, converted on the device
+// with OpenCV's fixed-point COLOR_BGR2GRAY.  Replaces the host-side cv::cvtColor of include/async_image_loader.h:68-69.
+extern "C" int svo_gpu_upload_bgr_batch(svo_gpu_ctx* ctx, int slot, const uint8_t* images, int mem_kind, int w, int h,
+                                        size_t stride_bytes, size_t image_stride_bytes, int batch)
+{
+    if (!ctx) return SVO_GPU_E_ARG;
+    if (int r = check_slot(ctx, slot)) return r;
+    if (!images) return fail(ctx, SVO_GPU_E_ARG, "images is null");
+    if (w < 1 || h < 1 || w > ctx->max_w || h > ctx->max_h)
+        return fail(ctx, SVO_GPU_E_ARG, "image %dx%d outside the context's 1..%dx1..%d", w, h, ctx->max_w, ctx->max_h);
+    if (batch < 1 || batch > ctx->max_batch) return fail(ctx, SVO_GPU_E_ARG, "batch %d outside 1..%d", batch, ctx->max_batch);
+    if (stride_bytes < 3 * (size_t)w) return fail(ctx, SVO_GPU_E_ARG, "stride %zu < 3 * width %d", stride_bytes, w);
+    if (batch > 1 && image_stride_bytes < stride_bytes * (size_t)h)
+        return fail(ctx, SVO_GPU_E_ARG, "image stride smaller than one image");
+    if (mem_kind != SVO_GPU_MEM_HOST && mem_kind != SVO_GPU_MEM_DEVICE) return fail(ctx, SVO_GPU_E_ARG, "mem_kind %d unknown", mem_kind);
+    DeviceGuard guard(ctx->device);
+    Slot& s = ctx->slots[slot];
+    const size_t pitch = round_up((size_t)w, 128), lane = pitch * (size_t)h;
+    if (int r = ensure(ctx, s.raw_own, round_up((size_t)ctx->max_w, 128) * (size_t)ctx->max_h * (size_t)ctx->max_batch + 64)) return r;
+    const uint8_t* src = images;
+    size_t src_pitch = stride_bytes, src_lane = image_stride_bytes;
+    if (mem_kind == SVO_GPU_MEM_HOST) {
+        const size_t row = 3 * (size_t)w;
+        if (int r = ensure(ctx, ctx->bgr_stage, 3 * (size_t)ctx->max_w * (size_t)ctx->max_h * (size_t)ctx->max_batch + 64)) return r;
+        uint8_t* d = static_cast<uint8_t*>(ctx->bgr_stage.p);
+        if (stride_bytes == row && (batch == 1 || image_stride_bytes == row * h))
+            CK(cudaMemcpyAsync(d, images, row * h * batch, cudaMemcpyHostToDevice, ctx->st));   // one contiguous copy
+        else
+            for (int b = 0; b < batch; ++b)
+                CK(cudaMemcpy2DAsync(d + b * row * h, row, images + b * image_stride_bytes, stride_bytes, row, (size_t)h,
+                                     cudaMemcpyHostToDevice, ctx->st));
+        src = d; src_pitch = row; src_lane = row * h;
+    }
+    launch_bgr2gray(ctx->st, src, src_pitch, src_lane, static_cast<uint8_t*>(s.raw_own.p), pitch, lane, w, h, batch, &ctx->launches);
+    CK(cudaGetLastError());
+    if (mem_kind == SVO_GPU_MEM_DEVICE) CK(cudaStreamSynchronize(ctx->st));   // the caller's buffer is free again on return
+    s.raw = static_cast<const uint8_t*>(s.raw_own.p);
+    s.raw_pitch = pitch; s.raw_lane = lane;
+    s.w = w; s.h = h; s.batch = batch;
+    s.uploaded = true;
+    s.pyr_built = false;
+    return 0;
+}
+
+extern "C" int svo_gpu_upload_bgr(svo_gpu_ctx* ctx, int slot, const uint8_t* host, int w, int h, size_t stride_bytes)
+{
+    return svo_gpu_upload_bgr_batch(ctx, slot, host, SVO_GPU_MEM_HOST, w, h, stride_bytes, stride_bytes * (size_t)(h > 0 ? h : 0), 1);
+}
+
+// the 8-bit gray image a slot holds (what the reference keeps as frame->leftImg() for its viewer and descriptors)
+extern "C" int svo_gpu_download_image(svo_gpu_ctx* ctx, int slot, int lane, uint8_t* host, size_t stride_bytes)
+{
+    if (!ctx) return SVO_GPU_E_ARG;
+    if (int r = check_slot(ctx, slot)) return r;
+    Slot& s = ctx->slots[slot];
+    if (!s.uploaded) return fail(ctx, SVO_GPU_E_STATE, "slot %d has no image", slot);
+    if (lane < 0 || lane >= s.batch) return fail(ctx, SVO_GPU_E_ARG, "lane %d out of range", lane);
+    if (!host || stride_bytes < (size_t)s.w) return fail(ctx, SVO_GPU_E_ARG, "host is null or stride %zu < width %d", stride_bytes, s.w);
+    DeviceGuard guard(ctx->device);
+    CK(cudaMemcpy2DAsync(host, stride_bytes, s.raw + (size_t)lane * s.raw_lane, s.raw_pitch, (size_t)s.w, (size_t)s.h,
+                         cudaMemcpyDeviceToHost, ctx->st));
+    CK(cudaStreamSynchronize(ctx->st));
+    return 0;
 }
 
 // enqueue only (no synchronisation): ingest + pyrDown chain of every lane of the slot

@@ -189,6 +189,52 @@ void launch_ingest(cudaStream_t st, const uint8_t* raw, size_t raw_pitch, size_t
     if (launches) ++*launches;
 }
 
+// ---- BGR -> gray (frame ingest of a colour sequence).  The reference's loader does cv::imread + cv::cvtColor(...,
+// COLOR_BGR2GRAY) on the host (include/async_image_loader.h:66-69); here the interleaved CV_8UC3 image goes over PCIe as it
+// is and the conversion runs on the way into the slot.  OpenCV's 8-bit fixed point, bit for bit:
+//   gray = (B 3735 + G 19235 + R 9798 + 2^14) >> 15            (oracle/svo_oracle.c:orc_bgr2gray, pinned against cv2)
+// HBM-bound: 3 bytes read + 1 written per pixel.  A thread makes 4 gray bytes from 12 source bytes: aligned 32-bit loads
+// + funnel shifts (any source alignment), consecutive lanes read consecutive 12-byte groups.
+__device__ __forceinline__ uint32_t gray15(uint32_t b, uint32_t g, uint32_t r)
+{
+    return (b * 3735u + g * 19235u + r * 9798u + (1u << 14)) >> 15;
+}
+
+__global__ void __launch_bounds__(128) bgr2gray_kernel(const uint8_t* __restrict__ src, size_t src_pitch, size_t src_lane,
+                                                       uint8_t* __restrict__ dst, size_t dst_pitch, size_t dst_lane, int w)
+{
+    const int q = blockIdx.x * 128 + threadIdx.x;   // 4-pixel group of the row
+    const int x = 4 * q;
+    if (x >= w) return;
+    const uint8_t* s = src + (size_t)blockIdx.z * src_lane + (size_t)blockIdx.y * src_pitch + 3 * (size_t)x;
+    uint32_t* d = reinterpret_cast<uint32_t*>(dst + (size_t)blockIdx.z * dst_lane + (size_t)blockIdx.y * dst_pitch) + q;
+    uint32_t out;
+    if (x + 4 <= w) {
+        const uintptr_t addr = reinterpret_cast<uintptr_t>(s);
+        const uint32_t* wp = reinterpret_cast<const uint32_t*>(addr & ~(uintptr_t)3);
+        const int sh = 8 * (int)(addr & 3);
+        const uint32_t w0 = __ldg(wp), w1 = __ldg(wp + 1), w2 = __ldg(wp + 2);
+        const uint32_t w3 = sh ? __ldg(wp + 3) : 0u;   // holds a needed byte exactly when the group is not word aligned
+        const uint32_t a = __funnelshift_r(w0, w1, sh), b = __funnelshift_r(w1, w2, sh), c = __funnelshift_r(w2, w3, sh);
+        out = gray15(a & 255u, (a >> 8) & 255u, (a >> 16) & 255u) |
+              gray15(a >> 24, b & 255u, (b >> 8) & 255u) << 8 |
+              gray15((b >> 16) & 255u, b >> 24, c & 255u) << 16 |
+              gray15((c >> 8) & 255u, (c >> 16) & 255u, c >> 24) << 24;
+    } else {   // ragged end of the row: byte loads, nothing beyond the last pixel is touched
+        out = 0;
+        for (int i = 0; x + i < w; ++i) out |= gray15(s[3 * i], s[3 * i + 1], s[3 * i + 2]) << (8 * i);
+    }
+    *d = out;   // the destination pitch is a multiple of 4 >= w rounded up, so the padding bytes of the last word exist
+}
+
+void launch_bgr2gray(cudaStream_t st, const uint8_t* src, size_t src_pitch, size_t src_lane, uint8_t* dst, size_t dst_pitch,
+                     size_t dst_lane, int w, int h, int batch, long long* launches)
+{
+    dim3 grid(((w + 3) / 4 + 127) / 128, h, batch);
+    bgr2gray_kernel<<<grid, 128, 0, st>>>(src, src_pitch, src_lane, dst, dst_pitch, dst_lane, w);
+    if (launches) ++*launches;
+}
+
 void launch_pyrdown(cudaStream_t st, uint8_t* pyr, const PyrGeom& g, int level, int batch, long long* launches)
 {
     const LevelGeom& S = g.lv[level - 1];

@@ -49,6 +49,9 @@ __host__ __device__ inline int reflect101(int i, int n)
 // raw image (pitch raw_pitch, lane stride raw_lane) -> padded level 0 of every lane
 void launch_ingest(cudaStream_t st, const uint8_t* raw, size_t raw_pitch, size_t raw_lane, uint8_t* pyr,
                    const PyrGeom& g, int batch, long long* launches);
+// interleaved BGR (CV_8UC3) -> gray rows of pitch dst_pitch (a multiple of 4, >= w rounded up to 4), every lane
+void launch_bgr2gray(cudaStream_t st, const uint8_t* src, size_t src_pitch, size_t src_lane, uint8_t* dst, size_t dst_pitch,
+                     size_t dst_lane, int w, int h, int batch, long long* launches);
 // level l-1 -> level l (5x5 Gaussian pyrDown, margins included), every lane
 void launch_pyrdown(cudaStream_t st, uint8_t* pyr, const PyrGeom& g, int level, int batch, long long* launches);
 

@@ -17,6 +17,7 @@
 #define CV_32F 5
 #define CV_MAKETYPE(depth, cn) ((depth) + (((cn) - 1) << 3))
 #define CV_8UC1 CV_MAKETYPE(CV_8U, 1)
+#define CV_8UC3 CV_MAKETYPE(CV_8U, 3)
 #define CV_32FC1 CV_MAKETYPE(CV_32F, 1)
 
 typedef unsigned char uchar;
@@ -97,7 +98,8 @@ public:
         data = own_.get();
     }
     int type() const { return type_; }
-    size_t elemSize() const { return (type_ & 7) == CV_32F ? 4 : 1; }
+    int channels() const { return (type_ >> 3) + 1; }
+    size_t elemSize() const { return ((type_ & 7) == CV_32F ? 4 : 1) * (size_t)channels(); }
     bool empty() const { return data == nullptr || rows == 0 || cols == 0; }
     Size size() const { return Size(cols, rows); }
     bool isContinuous() const { return step == (size_t)cols * elemSize(); }

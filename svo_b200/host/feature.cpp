@@ -35,9 +35,17 @@ constexpr int kMaxLevels = SVO_GPU_MAX_LEVELS;
     throw cv::Exception(std::string(where) + ": svo_gpu error " + std::to_string(rc) + ": " + svo_gpu_last_error(ctx));
 }
 
+// gray frames as the reference passes them, or BGR frames straight from cv::imread: the loader's cvtColor
+// (include/async_image_loader.h:68-69) then happens on the device, bit-identical to cv::COLOR_BGR2GRAY
 void check_image(const cv::Mat& m, const char* what)
 {
-    if (m.type() != CV_8UC1) throw cv::Exception(std::string(what) + " must be CV_8UC1");
+    if (m.type() != CV_8UC1 && m.type() != CV_8UC3) throw cv::Exception(std::string(what) + " must be CV_8UC1 or CV_8UC3 (BGR)");
+}
+
+int upload_image(svo_gpu_ctx* ctx, int slot, const cv::Mat& m)
+{
+    if (m.type() == CV_8UC3) return svo_gpu_upload_bgr(ctx, slot, m.data, m.cols, m.rows, m.step);
+    return svo_gpu_upload(ctx, slot, m.data, m.cols, m.rows, m.step);
 }
 
 }  // namespace
@@ -80,7 +88,7 @@ void run_fast(const cv::Mat& image, std::vector<cv::KeyPoint>& keypoints, Call&&
     int min_points = 0;
     for (int attempt = 0; attempt < 2; ++attempt) {
         svo_gpu_ctx* ctx = defaultContext(g_tab.device, image.cols, image.rows, min_points);
-        int rc = svo_gpu_upload(ctx, 0, image.data, image.cols, image.rows, image.step);
+        int rc = upload_image(ctx, 0, image);
         if (rc != SVO_GPU_OK) raise(ctx, "svo_gpu_upload", rc);
         const int cap = g_tab.by_device[g_tab.device].max_points;
         xy.resize(2 * (size_t)cap);
@@ -101,10 +109,23 @@ void run_fast(const cv::Mat& image, std::vector<cv::KeyPoint>& keypoints, Call&&
 
 }  // namespace
 
+void cvtColorBGR2GRAY(const cv::Mat& bgr, cv::Mat& gray)
+{
+    if (bgr.empty()) { gray = cv::Mat(); return; }
+    if (bgr.type() != CV_8UC3) throw cv::Exception("cvtColorBGR2GRAY: source must be CV_8UC3");
+    svo_gpu_ctx* ctx = defaultContext(g_tab.device, bgr.cols, bgr.rows, 0);
+    int rc = svo_gpu_upload_bgr(ctx, 0, bgr.data, bgr.cols, bgr.rows, bgr.step);
+    if (rc != SVO_GPU_OK) raise(ctx, "svo_gpu_upload_bgr", rc);
+    cv::Mat out(bgr.rows, bgr.cols, CV_8UC1);   // a fresh buffer: `gray` may be `bgr` itself, as in the loader
+    rc = svo_gpu_download_image(ctx, 0, 0, out.data, out.step);
+    if (rc != SVO_GPU_OK) raise(ctx, "svo_gpu_download_image", rc);
+    gray = out;
+}
+
 void detectFAST(const cv::Mat& image, std::vector<cv::KeyPoint>& keypoints, const cv::Mat& mask, int threshold, bool nms)
 {
     if (!mask.empty()) {
-        check_image(mask, "mask");
+        if (mask.type() != CV_8UC1) throw cv::Exception("mask must be CV_8UC1");
         if (mask.rows != image.rows || mask.cols != image.cols) throw cv::Exception("mask size differs from the image size");
     }
     run_fast(image, keypoints, [&](svo_gpu_ctx* ctx, float* xy, float* resp, int cap, int* count) {
@@ -160,8 +181,8 @@ void calcOpticalFlowPyrLK(const cv::Mat& prevImg, const cv::Mat& nextImg, const 
         throw cv::Exception("calcOpticalFlowPyrLK: maxLevel >= 0 && winSize.width > 2 && winSize.height > 2");
     svo_gpu_ctx* ctx = defaultContext(g_tab.device, prevImg.cols, prevImg.rows, n);
     int rc;
-    if ((rc = svo_gpu_upload(ctx, 0, prevImg.data, prevImg.cols, prevImg.rows, prevImg.step)) ||
-        (rc = svo_gpu_upload(ctx, 1, nextImg.data, nextImg.cols, nextImg.rows, nextImg.step)))
+    if ((rc = upload_image(ctx, 0, prevImg)) ||
+        (rc = upload_image(ctx, 1, nextImg)))
         raise(ctx, "svo_gpu_upload", rc);
     const int ml = std::min(maxLevel, kMaxLevels - 1);
     if ((rc = svo_gpu_build_pyramid(ctx, 0, winSize.width, winSize.height, ml, nullptr)) ||
@@ -182,7 +203,7 @@ namespace {
 void upload_pair(svo_gpu_ctx* ctx, const cv::Mat& a, const cv::Mat& b, int win, int max_level)
 {
     int rc;
-    if ((rc = svo_gpu_upload(ctx, 0, a.data, a.cols, a.rows, a.step)) || (rc = svo_gpu_upload(ctx, 1, b.data, b.cols, b.rows, b.step)))
+    if ((rc = upload_image(ctx, 0, a)) || (rc = upload_image(ctx, 1, b)))
         raise(ctx, "svo_gpu_upload", rc);
     if ((rc = svo_gpu_build_pyramid(ctx, 0, win, win, max_level, nullptr)) || (rc = svo_gpu_build_pyramid(ctx, 1, win, win, max_level, nullptr)))
         raise(ctx, "svo_gpu_build_pyramid", rc);

@@ -117,6 +117,26 @@ int main(int argc, char** argv)
         std::vector<cv::KeyPoint> kp3(3);
         mDetector->detect(cv::Mat(), kp3);
         put_i(fo, (int)(out.size() + st.size() + kp3.size() + (er.empty() ? 0 : 1)));
+        // ---- colour frames (include/async_image_loader.h:66-69): BGR = (a, b, 255 - a); the device-side cvtColor, and the
+        //      detector fed the CV_8UC3 frame directly, must agree with the gray path
+        {
+            cv::Mat bgr(h, w, CV_8UC3), gray;
+            for (int y = 0; y < h; ++y)
+                for (int x = 0; x < w; ++x) {
+                    uchar* p = bgr.ptr<uchar>(y) + 3 * x;
+                    p[0] = a.at<uchar>(y, x); p[1] = b.at<uchar>(y, x); p[2] = (uchar)(255 - a.at<uchar>(y, x));
+                }
+            svo::cvtColorBGR2GRAY(bgr, gray);
+            put(fo, gray.data, (size_t)w * h);
+            std::vector<cv::KeyPoint> kg, kc;
+            mDetector->detect(gray, kg);
+            mDetector->detect(bgr, kc);
+            int same_c = kg.size() == kc.size();
+            for (size_t i = 0; same_c && i < kg.size(); ++i)
+                same_c = kg[i].pt.x == kc[i].pt.x && kg[i].pt.y == kc[i].pt.y && kg[i].response == kc[i].response;
+            put_i(fo, same_c);
+            put_i(fo, (int)kg.size());
+        }
     } catch (const cv::Exception& e) {
         fprintf(stderr, "frontend_selftest: %s\n", e.what());
         fclose(fo);

@@ -73,6 +73,11 @@ void detectFAST(const cv::Mat& image, std::vector<cv::KeyPoint>& keypoints, cons
 void detectFASTAvoiding(const cv::Mat& image, const std::vector<cv::Point2f>& tracked, float half,
                         std::vector<cv::KeyPoint>& keypoints, int threshold, bool nms);
 
+// cv::cvtColor(bgr, gray, cv::COLOR_BGR2GRAY) for CV_8UC3 frames, computed on the device, bit-identical to OpenCV's 8-bit
+// fixed point: the conversion the reference's loader applies to the colour sequence (include/async_image_loader.h:68-69).
+// Every image argument below also accepts the CV_8UC3 frame itself (converted on the way in), which saves this round trip.
+void cvtColorBGR2GRAY(const cv::Mat& bgr, cv::Mat& gray);
+
 // cv::calcOpticalFlowPyrLK with its full parameter list and defaults.  status: 0/1 per point; err: CV_32F n x 1.
 // OPTFLOW_USE_INITIAL_FLOW is not supported (the reference never sets it) and throws.
 void calcOpticalFlowPyrLK(const cv::Mat& prevImg, const cv::Mat& nextImg, const std::vector<cv::Point2f>& prevPts,

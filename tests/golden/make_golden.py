@@ -73,6 +73,18 @@ def golden_pyramid():
     np.savez_compressed(os.path.join(HERE, "pyramid.npz"), **out)
 
 
+def golden_bgr():
+    """cv::cvtColor(BGR2GRAY) as the reference's loader applies it (include/async_image_loader.h:68-69)."""
+    rng = np.random.default_rng(51)
+    rnd = rng.integers(0, 256, size=(37, 61, 3), dtype=np.uint8)                     # odd sizes: ragged row tails
+    vals = np.array([0, 1, 2, 127, 128, 129, 254, 255], np.uint8)
+    B, G, R = np.meshgrid(np.arange(256, dtype=np.uint8), vals, vals, indexing="ij")
+    extreme = np.ascontiguousarray(np.stack([B, G, R], -1).reshape(256, 64, 3))       # every B x extreme G, R
+    out = {"rnd": rnd, "rnd_gray": cv2.cvtColor(rnd, cv2.COLOR_BGR2GRAY),
+           "extreme": extreme, "extreme_gray": cv2.cvtColor(extreme, cv2.COLOR_BGR2GRAY)}
+    np.savez_compressed(os.path.join(HERE, "bgr.npz"), **out)
+
+
 def golden_klt():
     a, b = small_pair(200, 150, 41)
     xy, _ = O.cv2_fast(a, 20, True)
@@ -115,6 +127,7 @@ if __name__ == "__main__":
     assert O.have_ref_bucket(), "oracle/_ref/libref_bucket.so missing (needs /root/reference)"
     n = golden_fast()
     golden_pyramid()
+    golden_bgr()
     golden_klt()
     golden_bucket()
     with open(os.path.join(HERE, "VERSIONS.txt"), "w") as f:

@@ -101,4 +101,9 @@ def test_wrappers_match_oracle(exe, oracle, tmp_path):
     keep = np.nonzero((rst != 0) & (np.abs(rxy[:, 1] - oxy[:, 1]) < np.float32(0.9)))[0]
     assert m == len(keep) and np.array_equal(lp, oxy[keep]) and np.array_equal(rp, rxy[keep])
     assert int(take(np.int32, 1)[0]) == 0                    # empty inputs -> empty outputs, like OpenCV
+    # colour frames: device-side cvtColor(BGR2GRAY) of (a, b, 255 - a), and detect() fed the CV_8UC3 frame directly
+    gray = take(np.uint8, w * h).reshape(h, w)
+    assert np.array_equal(gray, oracle.orc_bgr2gray(np.stack([a, b, 255 - a], axis=-1)))
+    assert int(take(np.int32, 1)[0]) == 1
+    assert int(take(np.int32, 1)[0]) == len(oracle.orc_fast(gray, 20, True)[0])
     assert off == len(buf)
