@@ -317,9 +317,10 @@ def run_b200(args):
     kernels = {n: {"ms": float(stage_ms[i]), "alg_bytes": float(alg[n]),
                    "achieved_gbs": float(alg[n] / (stage_ms[i] * 1e-3) / 1e9) if stage_ms[i] > 0 else None}
                for i, n in enumerate(names)}
-    traffic = None
+    traffic = ncu = None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get("klt_kernel")
+        ncu = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        traffic = ncu.get("klt_kernel")
     except Exception:
         pass
     klt = kernels["klt"]
@@ -339,7 +340,8 @@ def run_b200(args):
         "roofline": {"kernel": "klt_kernel<21,21,8>", "bound": "hbm", "achieved": klt["achieved_gbs"], "peak": hbm_peak,
                      "unit": "GB/s", "frac": (klt["achieved_gbs"] or 0) / hbm_peak, "traffic": traffic,
                      "peak_source": peak_src,
-                     "note": "LK is not HBM-bound: its footprint (two pyramids) lives in L2; see klt_issue_model"},
+                     "note": "LK is not HBM-bound: its footprint (two pyramids) lives in L2; its bound is the SM issue "
+                             "rate, see roofline.issue and klt_issue_model"},
         "klt_issue_model": {"iterations_per_track": it_per_track, "lane_ops_per_launch": lane_ops,
                             "achieved_lane_ops_per_s": lane_ops / (klt["ms"] * 1e-3) if klt["ms"] > 0 else None,
                             "peak_lane_ops_per_s": 148 * 128 * sm_mhz * 1e6,
@@ -349,6 +351,14 @@ def run_b200(args):
                   "status_ok_frac": ok_sum / max(trk_sum, 1)},
     }
     line["klt_tracks_per_s"] = world * S * n_trk * K / (dev_ms * 1e-3)
+    # the bound LK actually runs against: warp instructions issued per second.  Instructions per launch come from the ncu
+    # capture of this same workload (profiles/ncu_traffic.json, 64 x 2000 tracks), the launch time is measured here.
+    if ncu and ncu.get("klt_warp_inst_per_launch") and S == 64 and wl["n_tracks"] == 2000 and klt["ms"] > 0:
+        peak_issue = 148 * 4 * sm_mhz * 1e6
+        ach = ncu["klt_warp_inst_per_launch"] / (klt["ms"] * 1e-3)
+        line["roofline"]["issue"] = {"bound": "sm issue slots", "achieved": ach, "peak": peak_issue, "unit": "warp-inst/s",
+                                     "frac": ach / peak_issue, "warp_inst_per_launch": ncu["klt_warp_inst_per_launch"],
+                                     "source": "instructions: ncu smsp__inst_executed.sum (profiles/); time: live CUDA events"}
     if world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
         ns = min(S, threads)

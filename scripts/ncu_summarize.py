@@ -65,6 +65,12 @@ def kernels():
                 for r in rows[2:] if pat in r[idx["Kernel Name"]]]
         if vals:
             tr[key] = max(vals)   # the level-0 launch for the per-level kernels
+    # warp instructions the LK launch executed and its issue utilisation under ncu -> bench.py's roofline.issue
+    for r in rows[2:]:
+        if "klt_run_kernel" in r[idx["Kernel Name"]]:
+            tr["klt_warp_inst_per_launch"] = float(r[idx["smsp__inst_executed.sum"]])
+            tr["klt_issue_active_pct_ncu"] = float(r[idx["smsp__issue_active.avg.pct_of_peak_sustained_active"]])
+            tr["klt_workload_note"] = "64 streams x 2000 tracks (bench.py default workload)"
     import json
     json.dump(tr, open(os.path.join(os.path.dirname(dst), "ncu_traffic.json"), "w"), indent=1)
     with open(dst + "_kernels.txt", "w") as f:

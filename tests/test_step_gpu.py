@@ -47,6 +47,27 @@ def test_step_matches_cpu_pipeline(oracle, mask_half):
         assert ctx.last_klt_iterations > 0
 
 
+def test_step_detection_beside_tracking(oracle, monkeypatch):
+    """SVO_GPU_STEP_OVERLAP=1 (read by svo_gpu_create): mask -> FAST -> bucketing on a second stream beside the LK kernel,
+    whose work queue is then served by a main and a helper launch.  Same answers as the back-to-back step, and the profiled
+    stage times stay meaningful."""
+    from oracle.cpu_pipeline import CpuFrontend
+    monkeypatch.setenv("SVO_GPU_STEP_OVERLAP", "1")
+    monkeypatch.setenv("SVO_GPU_KLT_RESERVE", "4")
+    seqs = _seqs()
+    B = seqs.shape[0]
+    with capi.Context(max_w=W, max_h=H, max_levels=4, max_points=8192, max_batch=B) as ctx:
+        fe = Frontend(ctx, W, H, B, kp_capacity=8192, bucket_capacity=2048, max_tracks=400, mask_half=10.0)
+        cpus = [CpuFrontend(fe.pdict, impl="orc") for _ in range(B)]
+        ctx.step_profile(True)
+        for t in range(seqs.shape[1]):
+            fe.step_host(np.ascontiguousarray(seqs[:, t]))
+            for b in range(B):
+                _check_lane(fe, b, cpus[b].step(seqs[b, t]), first=(t == 0))
+        ms = ctx.step_profile(False)
+        assert all(m > 0 for m in ms) and ctx.last_klt_iterations > 0
+
+
 def test_step_device_memory_and_reset(oracle):
     import torch
     from oracle.cpu_pipeline import CpuFrontend
