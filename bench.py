@@ -244,18 +244,34 @@ def run_b200(args):
     def max_over_ranks(ms):
         return sharding.max_over_ranks(ms, world, device="cuda")
 
-    # ---- end to end: host frames in, results out, every step.  svo_gpu_step_pipelined copies step i+1's frames (pinned host
-    #      memory) on a second stream while step i computes; every step still waits for its own results on the host.
+    # Both timed loops drive the step through svo_gpu_step_submit / svo_gpu_step_wait with two steps outstanding: step i+1 is
+    # enqueued before the host waits for step i (frame i+1 never needs frame i's results on the HOST: the tracks are re-seeded
+    # on the device), so the device does not idle while the host handles a frame.  Every step's results are waited for.
+    def run_steps(i0, i1, submit, after_wait=None):
+        for i in range(i0, i1):
+            submit(i)
+            if fe.outstanding == 2:
+                fe.wait()
+                if after_wait:
+                    after_wait()
+        while fe.outstanding:
+            fe.wait()
+            if after_wait:
+                after_wait()
+
+    # ---- end to end: host frames in, results out, every step.  Step i+1's frames (pinned host memory) are copied on a second
+    #      stream while step i computes; every step's results land in pinned host arrays before its wait returns.
     def hptr(i):
         return host[i % RING].data_ptr()
 
+    def submit_host(i):
+        fe.submit(hptr(i), hptr(i + 1), capi.MEM_HOST, w, w * h)
+
     fe.reset()
-    for i in range(W):
-        fe.step_host_pipelined(hptr(i), hptr(i + 1), w, w * h)
+    run_steps(0, W, submit_host)
     barrier()
     ev[0].record(stream)
-    for i in range(W, W + K):
-        fe.step_host_pipelined(hptr(i), hptr(i + 1), w, w * h)
+    run_steps(W, W + K, submit_host)
     ev[1].record(stream)
     barrier()
     e2e_ms = max_over_ranks(ev[0].elapsed_time(ev[1]))
@@ -269,20 +285,24 @@ def run_b200(args):
 
     # ---- device resident: frames already in HBM, nothing returned to the host
     sampler = ClockSampler(local) if rank == 0 else None   # nvidia-smi needs a moment to start: launched before the warm-up
+    def submit_dev(i):
+        fe.submit(dev[i % RING].data_ptr(), None, capi.MEM_DEVICE, pitch, h * pitch, with_outputs=False)
+
     fe.reset()
-    for i in range(W):
-        fe.step_device(dev[i % RING].data_ptr(), pitch, h * pitch)
+    run_steps(0, W, submit_dev)
     ctx.step_profile(True)
     launches0 = ctx.launch_count
     barrier()
     t_start = time.time()
     ev[2].record(stream)
-    stage = np.zeros(4)
-    iters = 0
-    for i in range(W, W + K):
-        fe.step_device(dev[i % RING].data_ptr(), pitch, h * pitch)
-        stage += np.array(ctx.step_profile(True))
-        iters += ctx.last_klt_iterations
+    acc = {"stage": np.zeros(4), "iters": 0}
+
+    def after_wait():
+        acc["stage"] += np.array(ctx.step_profile(True))
+        acc["iters"] += ctx.last_klt_iterations
+
+    run_steps(W, W + K, submit_dev, after_wait)
+    stage, iters = acc["stage"], acc["iters"]
     ev[3].record(stream)
     barrier()
     clocks = sampler.stop(t_start, time.time()) if sampler else None
@@ -351,6 +371,7 @@ def run_b200(args):
                   "status_ok_frac": ok_sum / max(trk_sum, 1)},
     }
     line["klt_tracks_per_s"] = world * S * n_trk * K / (dev_ms * 1e-3)
+    line["config"]["pipelining"] = "svo_gpu_step_submit / _wait, 2 steps outstanding; every step's results are waited for"
     # the bound LK actually runs against: warp instructions issued per second.  Instructions per launch come from the ncu
     # capture of this same workload (profiles/ncu_traffic.json, 64 x 2000 tracks), the launch time is measured here.
     if ncu and ncu.get("klt_warp_inst_per_launch") and S == 64 and wl["n_tracks"] == 2000 and klt["ms"] > 0:

@@ -40,6 +40,7 @@ extern "C" {
 #define SVO_GPU_E_STATE (-5)       /* slot not uploaded / pyramid not built (or built for a smaller window) */
 
 #define SVO_GPU_NUM_SLOTS 4
+#define SVO_GPU_STEP_DEPTH 2   /* steps that may be outstanding between svo_gpu_step_submit and svo_gpu_step_wait */
 #define SVO_GPU_MAX_LEVELS 8       /* pyramid levels 0..7 (OpenCV maxLevel <= 7) */
 #define SVO_GPU_MAX_WIN 45         /* largest LK window side */
 
@@ -245,6 +246,19 @@ SVO_GPU_API int svo_gpu_step(svo_gpu_ctx* ctx, const uint8_t* images, int mem_ki
 SVO_GPU_API int svo_gpu_step_pipelined(svo_gpu_ctx* ctx, const uint8_t* images, const uint8_t* next_images, int mem_kind,
                                        size_t stride_bytes, size_t image_stride_bytes, int batch,
                                        const svo_gpu_step_params* params, const svo_gpu_step_outputs* outputs_or_null);
+/* The same step split in two, for callers that keep the GPU busy across frames (the reference's loop body, src/tracking.cpp:
+ * 240-257, consumes frame t's results on the host while the loader thread already holds frame t+1): _submit enqueues the whole
+ * step and returns at once with a ticket; _wait(ticket) blocks until that step is through, fills the n_* counts and reports
+ * capacity errors.  Up to SVO_GPU_STEP_DEPTH steps may be outstanding, waited for in submission order.  Frame t+1 never
+ * needs frame t's results on the HOST (tracks are re-seeded on the device), so submit(t+1) before wait(t) is legal and keeps
+ * the device from idling while the host handles frame t.  The caller keeps `images` (device memory), `next_images` and the
+ * `outputs` arrays (pinned host memory for true overlap; a distinct set per outstanding step) alive until the wait.
+ * svo_gpu_step_pipelined(...) == submit + wait. */
+SVO_GPU_API int svo_gpu_step_submit(svo_gpu_ctx* ctx, const uint8_t* images, const uint8_t* next_images, int mem_kind,
+                                    size_t stride_bytes, size_t image_stride_bytes, int batch,
+                                    const svo_gpu_step_params* params, const svo_gpu_step_outputs* outputs_or_null,
+                                    int* ticket_out);
+SVO_GPU_API int svo_gpu_step_wait(svo_gpu_ctx* ctx, int ticket);
 /* Forgets the previous frame and tracks of every lane (start of a new set of sequences). */
 SVO_GPU_API int svo_gpu_step_reset(svo_gpu_ctx* ctx);
 /* Number of kernel launches (graph kernel nodes included) issued by this context so far. */

@@ -60,6 +60,9 @@ SYMBOLS = {
                                C.c_void_p]),
     "svo_gpu_step_pipelined": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_size_t, C.c_size_t, C.c_int,
                                          C.c_void_p, C.c_void_p]),
+    "svo_gpu_step_submit": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_size_t, C.c_size_t, C.c_int,
+                                      C.c_void_p, C.c_void_p, _i32p]),
+    "svo_gpu_step_wait": (C.c_int, [C.c_void_p, C.c_int]),
     "svo_gpu_step_reset": (C.c_int, [C.c_void_p]),
     "svo_gpu_launch_count": (C.c_longlong, [C.c_void_p]),
     "svo_gpu_step_profile": (C.c_int, [C.c_void_p, C.c_int, _f32p]),
@@ -336,6 +339,17 @@ class Context:
         self._ck(self.lib.svo_gpu_step_pipelined(self.h, C.c_void_p(images_ptr), C.c_void_p(next_ptr) if next_ptr else None,
                                                  mem_kind, stride, image_stride, batch, C.byref(params),
                                                  C.byref(outputs) if outputs is not None else None))
+
+    def step_submit(self, images_ptr, next_ptr, mem_kind, stride, image_stride, batch, params, outputs=None):
+        """Enqueues the step and returns its ticket; up to STEP_DEPTH may be outstanding (see svo_gpu.h)."""
+        t = C.c_int(-1)
+        self._ck(self.lib.svo_gpu_step_submit(self.h, C.c_void_p(images_ptr), C.c_void_p(next_ptr) if next_ptr else None,
+                                              mem_kind, stride, image_stride, batch, C.byref(params),
+                                              C.byref(outputs) if outputs is not None else None, C.byref(t)))
+        return t.value
+
+    def step_wait(self, ticket):
+        self._ck(self.lib.svo_gpu_step_wait(self.h, int(ticket)))
 
     def step_reset(self):
         self._ck(self.lib.svo_gpu_step_reset(self.h))

@@ -33,6 +33,18 @@ struct Slot {
     int win_w = 0, win_h = 0;
 };
 
+// one submitted step (svo_gpu_step_submit .. svo_gpu_step_wait): its pinned read-back scratch, events and output views
+struct StepTicket {
+    bool busy = false;
+    int* hs = nullptr;            // pinned, 4 * max_batch + 16 ints: tracked, keypoints, bucketed, bucket error flags, LK iterations
+    cudaEvent_t done = nullptr;
+    cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t eva[4] = {nullptr, nullptr, nullptr, nullptr};
+    svo_gpu_step_outputs out{};
+    bool has_out = false, prof = false, track = false, overlap = false;
+    int batch = 0, kp_cap = 0;
+};
+
 thread_local char g_create_error[512] = "";
 
 }  // namespace
@@ -80,7 +92,9 @@ struct svo_gpu_ctx {
     svo_gpu_step_params step_params{};
     int step_batch = 0;
     bool profile = false;
-    cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    StepTicket tickets[SVO_GPU_STEP_DEPTH];
+    int next_ticket = 0;
+    cudaEvent_t ev_raw_free[2] = {nullptr, nullptr};   // per step slot: the ingest that last read its raw frame is through
     // frame ingest pipelining: the next step's host frames are copied on a second stream while this step computes
     cudaStream_t copy_st = nullptr;
     cudaEvent_t ev_copy = nullptr;
@@ -90,7 +104,6 @@ struct svo_gpu_ctx {
     // SM free for them; a helper launch of the LK kernel on aux_st takes those slots over afterwards (same work queue)
     cudaStream_t aux_st = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
-    cudaEvent_t eva[4] = {nullptr, nullptr, nullptr, nullptr};
     int overlap = 0;        // SVO_GPU_STEP_OVERLAP (0 = one stream, stages back to back; 1 measured slower, gpurun_out/s6)
     int klt_reserve = 3;    // SVO_GPU_KLT_RESERVE
     int fast_small = 1;     // SVO_GPU_FAST_SMALL: 128-thread FAST CTAs in the overlapped step
@@ -249,7 +262,13 @@ static int create_buffers(svo_gpu_ctx* ctx)
         CK(cudaMemcpy(ctx->int_max, big.data(), sizeof(int) * B, cudaMemcpyHostToDevice));
     }
     CK(cudaMallocHost(reinterpret_cast<void**>(&ctx->h_small), sizeof(int) * (4 * B + 16)));
-    for (auto& e : ctx->ev) CK(cudaEventCreate(&e));
+    for (auto& tk : ctx->tickets) {
+        CK(cudaMallocHost(reinterpret_cast<void**>(&tk.hs), sizeof(int) * (4 * B + 16)));
+        CK(cudaEventCreateWithFlags(&tk.done, cudaEventDisableTiming));
+        for (auto& e : tk.ev) CK(cudaEventCreate(&e));
+        for (auto& e : tk.eva) CK(cudaEventCreate(&e));
+    }
+    for (auto& e : ctx->ev_raw_free) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     CK(cudaStreamCreateWithFlags(&ctx->copy_st, cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&ctx->ev_copy, cudaEventDisableTiming));
     CK(cudaStreamCreateWithFlags(&ctx->out_st, cudaStreamNonBlocking));
@@ -258,7 +277,6 @@ static int create_buffers(svo_gpu_ctx* ctx)
     CK(cudaStreamCreateWithFlags(&ctx->aux_st, cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
-    for (auto& e : ctx->eva) CK(cudaEventCreate(&e));
     if (const char* v = getenv("SVO_GPU_STEP_OVERLAP")) ctx->overlap = atoi(v);
     if (const char* v = getenv("SVO_GPU_KLT_RESERVE")) ctx->klt_reserve = atoi(v);
     if (const char* v = getenv("SVO_GPU_FAST_SMALL")) ctx->fast_small = atoi(v);
@@ -316,7 +334,13 @@ extern "C" int svo_gpu_destroy(svo_gpu_ctx* ctx)
     if (ctx->aux_st) { cudaStreamSynchronize(ctx->aux_st); cudaStreamDestroy(ctx->aux_st); }
     if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
     if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
-    for (auto& e : ctx->eva) if (e) cudaEventDestroy(e);
+    for (auto& tk : ctx->tickets) {
+        if (tk.hs) cudaFreeHost(tk.hs);
+        if (tk.done) cudaEventDestroy(tk.done);
+        for (auto& e : tk.ev) if (e) cudaEventDestroy(e);
+        for (auto& e : tk.eva) if (e) cudaEventDestroy(e);
+    }
+    for (auto& e : ctx->ev_raw_free) if (e) cudaEventDestroy(e);
     for (auto& s : ctx->slots) {
         cudaFree(s.raw_own.p);
         cudaFree(s.pyr.p);
@@ -328,8 +352,6 @@ extern "C" int svo_gpu_destroy(svo_gpu_ctx* ctx)
                     ctx->flt_b, ctx->flt_err, ctx->flt_n};
     for (void* p : bufs) cudaFree(p);
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
-    for (auto& e : ctx->ev)
-        if (e) cudaEventDestroy(e);
     if (ctx->st) cudaStreamDestroy(ctx->st);
     delete ctx;
     return 0;

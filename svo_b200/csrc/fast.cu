@@ -12,7 +12,7 @@
 //   fast_tile_kernel   one CTA per 128x32 tile: image tile + 4 px halo staged in shared memory, packed pre-test, segment test on the
 //                      candidates over the (128+2)x(32+2) score region, dense pass over the surviving corners for the score, NMS, and
 //                      a per-(row, tile) segment of kept keypoints written in x order via warp ballots.
-//   fast_gather_kernel one CTA per image row: offset = keypoints in all earlier rows (sum of the per-row counters) +
+//   fast_gather_kernel one warp per image row: offset = keypoints in all earlier rows (sum of the per-row counters) +
 //                      segments to the left; copies the segments to the final (x, y, response) list.
 #include <type_traits>
 
@@ -227,56 +227,52 @@ __global__ void __launch_bounds__(NT) fast_tile_kernel(const uint8_t* __restrict
     }
 }
 
-// grid = (h, batch), 128 threads
-__global__ void __launch_bounds__(128) fast_gather_kernel(int w, int h, int t, int nms, FastBufs fb, int ntx)
+// grid = (ceil(h / 8), batch), 256 threads: a warp owns an image row and never meets the other warps (no barrier, no shared
+// memory).  Row offset = keypoints in all earlier rows; segment offsets by a warp scan of the row's per-tile counts.
+constexpr int kGatherRows = 8;
+__global__ void __launch_bounds__(kGatherRows * 32) fast_gather_kernel(int w, int h, int t, int nms, FastBufs fb, int ntx)
 {
-    __shared__ int red[4];
-    __shared__ int segoff[1024];
-    const int y = blockIdx.x, lane_id = blockIdx.y;
-    const int tid = threadIdx.x, warp = tid >> 5, ln = tid & 31;
+    const int ln = threadIdx.x & 31;
+    const int y = blockIdx.x * kGatherRows + (threadIdx.x >> 5), lane_id = blockIdx.y;
+    if (y >= h) return;
     const int* rt = fb.rowtotal + (size_t)lane_id * fb.rows_cap;
 
-    int part = 0;
-    for (int i = tid; i < y; i += 128) part += rt[i];
+    int base = 0;
+    for (int i = ln; i < y; i += 32) base += rt[i];
 #pragma unroll
-    for (int o = 16; o; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
-    if (ln == 0) red[warp] = part;
-    __syncthreads();
-    const int base = red[0] + red[1] + red[2] + red[3];
+    for (int o = 16; o; o >>= 1) base += __shfl_xor_sync(0xffffffffu, base, o);
     const int mine = rt[y];
-    if (y == h - 1 && tid == 0) fb.kp_count[lane_id] = base + mine;
+    if (y == h - 1 && ln == 0) fb.kp_count[lane_id] = base + mine;
     if (mine == 0) return;
 
     const size_t seg0 = (size_t)lane_id * fb.rows_cap * fb.ntx_cap + (size_t)y * ntx;
-    if (warp == 0) {   // exclusive scan of the row's segment counts
-        int carry = 0;
-        for (int s0 = 0; s0 < ntx; s0 += 32) {
-            const int s = s0 + ln;
-            const int c = s < ntx ? (int)fb.segcnt[seg0 + s] : 0;
-            int inc = c;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const int v = __shfl_up_sync(0xffffffffu, inc, o);
-                if (ln >= o) inc += v;
-            }
-            if (s < ntx) segoff[s] = carry + inc - c;
-            carry += __shfl_sync(0xffffffffu, inc, 31);
-        }
-    }
-    __syncthreads();
-
     float2* oxy = fb.kp_xy + (size_t)lane_id * fb.kp_cap;
     float* orp = fb.kp_resp + (size_t)lane_id * fb.kp_cap;
-    for (int s = warp; s < ntx; s += 4) {
-        const int c = fb.segcnt[seg0 + s];
-        for (int j = ln; j < c; j += 32) {
-            const uint32_t e = fb.segkp[(seg0 + s) * TW + j];
-            const int idx = base + segoff[s] + j;
-            if (idx < fb.kp_cap) {
-                oxy[idx] = make_float2((float)(s * TW + (int)(e & 255u)), (float)y);
-                orp[idx] = nms ? (float)((int)(e >> 8) + t - 1) : 0.f;   // stored byte = best - t, score = best - 1
+    const float fy = (float)y;
+    for (int s0 = 0; s0 < ntx; s0 += 32) {
+        const int s = s0 + ln;
+        const int c = s < ntx ? (int)fb.segcnt[seg0 + s] : 0;
+        int inc = c;   // inclusive scan of the counts of these 32 segments
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, inc, o);
+            if (ln >= o) inc += v;
+        }
+        const int nseg = min(32, ntx - s0);
+        for (int k = 0; k < nseg; ++k) {   // warp-uniform loop: the lanes copy segment s0 + k together
+            const int ck = __shfl_sync(0xffffffffu, c, k);
+            if (ck == 0) continue;
+            const int ok = base + __shfl_sync(0xffffffffu, inc, k) - ck;
+            for (int j = ln; j < ck; j += 32) {
+                const uint32_t e = fb.segkp[(seg0 + s0 + k) * TW + j];
+                const int idx = ok + j;
+                if (idx < fb.kp_cap) {
+                    oxy[idx] = make_float2((float)((s0 + k) * TW + (int)(e & 255u)), fy);
+                    orp[idx] = nms ? (float)((int)(e >> 8) + t - 1) : 0.f;   // stored byte = best - t, score = best - 1
+                }
             }
         }
+        base += __shfl_sync(0xffffffffu, inc, 31);
     }
 }
 
@@ -324,7 +320,7 @@ void launch_fast(cudaStream_t st, const uint8_t* raw, size_t raw_pitch, size_t r
     else
         fast_tile_kernel<256><<<grid, 256, 0, st>>>(raw, raw_pitch, raw_lane, w, h, threshold, nms, mask, mask_pitch, mask_lane,
                                                     fb, ntx);
-    fast_gather_kernel<<<dim3(h, batch), 128, 0, st>>>(w, h, threshold, nms, fb, ntx);
+    fast_gather_kernel<<<dim3((h + kGatherRows - 1) / kGatherRows, batch), kGatherRows * 32, 0, st>>>(w, h, threshold, nms, fb, ntx);
     if (launches) *launches += 2;
 }
 

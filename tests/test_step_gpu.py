@@ -114,6 +114,65 @@ def test_step_pipelined_ingest(oracle):
                     _check_lane(fe, b, cpus[b].step(seqs[b, t]), first=(t == 0))
 
 
+@pytest.mark.parametrize("mem", ["host", "device"])
+def test_step_submit_wait(oracle, mem):
+    """svo_gpu_step_submit / svo_gpu_step_wait with two steps outstanding (submit(t + 1) before wait(t)): each step's
+    results, read after ITS wait, equal the synchronous CPU pipeline; host frames are prefetched one step ahead."""
+    import torch
+    from oracle.cpu_pipeline import CpuFrontend
+    seqs = _seqs(6)
+    B, T = seqs.shape[0], seqs.shape[1]
+    frames = torch.from_numpy(np.ascontiguousarray(seqs.transpose(1, 0, 2, 3)))           # [t, lane, h, w]
+    frames = frames.pin_memory() if mem == "host" else frames.cuda()
+    kind = capi.MEM_HOST if mem == "host" else capi.MEM_DEVICE
+    with capi.Context(max_w=W, max_h=H, max_levels=4, max_points=8192, max_batch=B) as ctx:
+        fe = Frontend(ctx, W, H, B, kp_capacity=8192, bucket_capacity=2048, max_tracks=400, mask_half=10.0)
+        cpus = [CpuFrontend(fe.pdict, impl="orc") for _ in range(B)]
+
+        def submit(t):
+            nxt = frames[t + 1].data_ptr() if (mem == "host" and t + 1 < T) else None
+            return fe.submit(frames[t].data_ptr(), nxt, kind, W, W * H)
+
+        def check(t):
+            fe.wait()
+            for b in range(B):
+                _check_lane(fe, b, cpus[b].step(seqs[b, t]), first=(t == 0))
+
+        submit(0)
+        for t in range(1, T):
+            submit(t)
+            assert fe.outstanding == 2
+            check(t - 1)
+        check(T - 1)
+        assert fe.outstanding == 0 and ctx.last_klt_iterations > 0
+
+
+def test_step_submit_wait_errors():
+    seqs = _seqs(1)
+    img = np.ascontiguousarray(seqs[:, 0])
+    with capi.Context(max_w=W, max_h=H, max_levels=4, max_points=8192, max_batch=3) as ctx:
+        fe = Frontend(ctx, W, H, 3, kp_capacity=0, bucket_capacity=2048, max_tracks=400)
+        t0 = fe.submit(img.ctypes.data, None, capi.MEM_HOST, W, W * H)
+        t1 = fe.submit(img.ctypes.data, None, capi.MEM_HOST, W, W * H)
+        with pytest.raises(capi.SvoGpuError) as e:                       # a third step while two are outstanding
+            ctx.step_submit(img.ctypes.data, None, capi.MEM_HOST, W, W * H, 3, fe.params, None)
+        assert e.value.code == capi.E_STATE
+        ctx.step_wait(t0)
+        with pytest.raises(capi.SvoGpuError) as e:                       # waited for twice
+            ctx.step_wait(t0)
+        assert e.value.code == capi.E_STATE
+        with pytest.raises(capi.SvoGpuError):                            # never issued
+            ctx.step_wait(t1 + 5)
+        ctx.step_wait(t1)
+        fe.reset()                                                       # a reset drops what is outstanding
+        t2 = fe.submit(img.ctypes.data, None, capi.MEM_HOST, W, W * H)
+        fe.reset()
+        with pytest.raises(capi.SvoGpuError):
+            ctx.step_wait(t2)
+        fe.step_host(img)                                                # and the synchronous call still works
+        assert int(fe.n_keypoints.sum()) > 0
+
+
 def test_step_capacity_error():
     seqs = _seqs(1)
     with capi.Context(max_w=W, max_h=H, max_levels=4, max_points=8192, max_batch=3) as ctx:
