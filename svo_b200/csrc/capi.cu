@@ -74,6 +74,7 @@ struct svo_gpu_ctx {
     uint8_t* trk_status = nullptr;
     float* trk_err = nullptr;
     int* trk_n = nullptr;         // [B]
+    int* step_summary = nullptr;  // [3][B] keypoints, bucketed, bucket error flags of the step (one read-back)
     int* int_max = nullptr;       // [B] all INT_MAX: "n is given by n_max" for the host-pointer calls
     unsigned long long* d_iters = nullptr;
     long long last_iters = 0;
@@ -249,6 +250,7 @@ static int create_buffers(svo_gpu_ctx* ctx)
     if (int r = dmalloc(ctx, ctx->trk_err, B * NP)) return r;
     if (int r = dmalloc(ctx, ctx->trk_n, B)) return r;
     if (int r = dmalloc(ctx, ctx->int_max, B)) return r;
+    if (int r = dmalloc(ctx, ctx->step_summary, 3 * B)) return r;
     if (int r = dmalloc(ctx, ctx->d_iters, 2)) return r;   // [0] LK iterations, [1] LK work counter
     if (int r = dmalloc(ctx, ctx->flt_index, B * NP)) return r;
     if (int r = dmalloc(ctx, ctx->flt_a, B * NP)) return r;
@@ -348,7 +350,7 @@ extern "C" int svo_gpu_destroy(svo_gpu_ctx* ctx)
     void* bufs[] = {ctx->fb.rowtotal, ctx->fb.segcnt, ctx->fb.segkp, ctx->fb.kp_xy, ctx->fb.kp_resp, ctx->fb.kp_count,
                     ctx->mask.p, ctx->bgr_stage.p, ctx->bb.out_xy, ctx->bb.out_age, ctx->bb.out_count, ctx->bb.err_flag, ctx->cell_slots.p,
                     ctx->cell_cnt.p, ctx->cell_last.p, ctx->bk_in_xy, ctx->bk_in_age, ctx->trk_xy, ctx->nxt_xy,
-                    ctx->trk_status, ctx->trk_err, ctx->trk_n, ctx->int_max, ctx->d_iters, ctx->flt_index, ctx->flt_a,
+                    ctx->trk_status, ctx->trk_err, ctx->trk_n, ctx->int_max, ctx->step_summary, ctx->d_iters, ctx->flt_index, ctx->flt_a,
                     ctx->flt_b, ctx->flt_err, ctx->flt_n};
     for (void* p : bufs) cudaFree(p);
     if (ctx->h_small) cudaFreeHost(ctx->h_small);

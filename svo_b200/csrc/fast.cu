@@ -258,16 +258,24 @@ __global__ void __launch_bounds__(kGatherRows * 32) fast_gather_kernel(int w, in
             const int v = __shfl_up_sync(0xffffffffu, inc, o);
             if (ln >= o) inc += v;
         }
-        const int nseg = min(32, ntx - s0);
-        for (int k = 0; k < nseg; ++k) {   // warp-uniform loop: the lanes copy segment s0 + k together
-            const int ck = __shfl_sync(0xffffffffu, c, k);
-            if (ck == 0) continue;
-            const int ok = base + __shfl_sync(0xffffffffu, inc, k) - ck;
-            for (int j = ln; j < ck; j += 32) {
-                const uint32_t e = fb.segkp[(seg0 + s0 + k) * TW + j];
-                const int idx = ok + j;
+        // the entries of these segments, flattened: output position p of the chunk lies in the first segment whose
+        // inclusive count exceeds p (binary search over the lanes' scan values), so all loads of a round are independent
+        const int tot = __shfl_sync(0xffffffffu, inc, 31);
+        for (int p0 = 0; p0 < tot; p0 += 32) {
+            const int p = p0 + ln;
+            int lo = 0, hi = 31;
+#pragma unroll
+            for (int it = 0; it < 5; ++it) {
+                const int mid = (lo + hi) >> 1;
+                if (__shfl_sync(0xffffffffu, inc, mid) > p) hi = mid;
+                else lo = mid + 1;
+            }
+            const int j = p - (__shfl_sync(0xffffffffu, inc, lo) - __shfl_sync(0xffffffffu, c, lo));
+            if (p < tot) {
+                const uint32_t e = fb.segkp[(seg0 + s0 + lo) * TW + j];
+                const int idx = base + p;
                 if (idx < fb.kp_cap) {
-                    oxy[idx] = make_float2((float)((s0 + k) * TW + (int)(e & 255u)), fy);
+                    oxy[idx] = make_float2((float)((s0 + lo) * TW + (int)(e & 255u)), fy);
                     orp[idx] = nms ? (float)((int)(e >> 8) + t - 1) : 0.f;   // stored byte = best - t, score = best - 1
                 }
             }
