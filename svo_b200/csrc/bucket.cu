@@ -18,6 +18,8 @@
 //   entry by summing min(m, k) over all earlier entries (a few thousand L2 reads), scans its own, and gathers.
 #include <limits.h>
 
+#include <algorithm>
+
 #include "svo_internal.cuh"
 
 namespace svo {
@@ -53,6 +55,21 @@ __global__ void __launch_bounds__(256) bucket_insert_kernel(const float2* __rest
             if (old > v) v = old;
         }
     }
+}
+
+// all per-call state of every lane in one launch: slots = empty, counts = 0, largest index = -1, error flag = 0
+__global__ void __launch_bounds__(256) bucket_clear_kernel(BucketBufs bb, int batch)
+{
+    const size_t nslots = bb.slots_cap * (size_t)batch, ncells = bb.cells_cap * (size_t)batch;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nslots; i += stride) bb.cell_slots[i] = kEmpty;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < ncells; i += stride) {
+        bb.cell_cnt[i] = 0;
+        bb.cell_last[i] = -1;
+    }
+    if (blockIdx.x == 0 && threadIdx.x < batch) bb.err_flag[threadIdx.x] = 0;
+    if (blockIdx.x == 0)
+        for (int i = threadIdx.x + 256; i < batch; i += 256) bb.err_flag[i] = 0;
 }
 
 __device__ __forceinline__ int emit_count(const int* __restrict__ cnt, int e, int Wc, int k)
@@ -131,23 +148,30 @@ __global__ void __launch_bounds__(256) bucket_emit_kernel(const float2* __restri
 
 void launch_bucket(cudaStream_t st, const float2* in_xy, const int* in_age, size_t in_lane, const int* n_dev, int n_max,
                    int img_w, int img_h, int bucket_size, int per_bucket, const BucketBufs& bb, int batch,
-                   long long* launches)
+                   long long* launches, int n_hint)
 {
     const int Hc = img_h / bucket_size, Wc = img_w / bucket_size;
     const int nb = (Hc + 1) * (Wc + 1);
     const int k = per_bucket;
-    // whole-batch clears (lanes are contiguous)
-    cudaMemsetAsync(bb.cell_slots, 0x7f, sizeof(int) * bb.slots_cap * batch, st);
-    cudaMemsetAsync(bb.cell_cnt, 0, sizeof(int) * bb.cells_cap * batch, st);
-    cudaMemsetAsync(bb.cell_last, 0xff, sizeof(int) * bb.cells_cap * batch, st);
-    cudaMemsetAsync(bb.err_flag, 0, sizeof(int) * batch, st);
-    int nblk = (n_max + 255) / 256;
-    nblk = nblk < 1 ? 1 : (nblk > 592 ? 592 : nblk);   // 148 SMs x 4
     static bool once = false;
-    if (!once) { prefer_max_shared(bucket_insert_kernel); prefer_max_shared(bucket_emit_kernel); once = true; }
+    if (!once) {
+        prefer_max_shared(bucket_insert_kernel); prefer_max_shared(bucket_emit_kernel); prefer_max_shared(bucket_clear_kernel);
+        once = true;
+    }
+    // whole-batch clear (lanes are contiguous), one launch
+    {
+        const size_t n = bb.slots_cap * (size_t)batch;
+        const int blocks = (int)std::min<size_t>((n + 1023) / 1024, 1184);   // 4 elements per thread, at most 148 x 8 CTAs
+        bucket_clear_kernel<<<std::max(blocks, 1), 256, 0, st>>>(bb, batch);
+    }
+    // the grid covers the expected list length (n_hint, when the caller has one) -- the grid-stride loop of the kernel
+    // makes any grid correct, a tighter one only spares CTAs that would find nothing to do
+    const int n_grid = n_hint > 0 ? std::min(n_max, n_hint) : n_max;
+    int nblk = (n_grid + 255) / 256;
+    nblk = nblk < 1 ? 1 : (nblk > 592 ? 592 : nblk);   // 148 SMs x 4
     bucket_insert_kernel<<<dim3(nblk, batch), 256, 0, st>>>(in_xy, in_lane, n_dev, n_max, Wc, nb, bucket_size, k, bb);
     bucket_emit_kernel<<<dim3((nb + 255) / 256, batch), 256, 0, st>>>(in_xy, in_age, in_lane, Wc, nb, k, bb);
-    if (launches) *launches += 2;
+    if (launches) *launches += 3;
 }
 
 }  // namespace svo

@@ -95,6 +95,7 @@ struct svo_gpu_ctx {
     bool profile = false;
     StepTicket tickets[SVO_GPU_STEP_DEPTH];
     int next_ticket = 0;
+    int kp_hint = 0;              // keypoints per lane seen by the last completed step (+25 %), 0 = unknown
     cudaEvent_t ev_raw_free[2] = {nullptr, nullptr};   // per step slot: the ingest that last read its raw frame is through
     // frame ingest pipelining: the next step's host frames are copied on a second stream while this step computes
     cudaStream_t copy_st = nullptr;

@@ -99,7 +99,7 @@ struct BucketBufs {
 // n per lane = min(n_dev[lane], n_max)
 void launch_bucket(cudaStream_t st, const float2* in_xy, const int* in_age, size_t in_lane, const int* n_dev, int n_max,
                    int img_w, int img_h, int bucket_size, int per_bucket, const BucketBufs& bb, int batch,
-                   long long* launches);
+                   long long* launches, int n_hint = 0);
 
 // ------------------------------------------------------------------------------------------------ klt.cu
 struct KltArgs {
