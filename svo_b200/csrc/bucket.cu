@@ -144,6 +144,100 @@ __global__ void __launch_bounds__(256) bucket_emit_kernel(const float2* __restri
     if (e == nemit - 1) bb.out_count[lane_id] = off + m;   // required output length (may exceed out_cap)
 }
 
+// ---- one CTA per lane, the whole bucket table of the lane in shared memory: clear, insert and emit in one launch.
+// Same formulation as the three kernels above (count, k smallest indices by atomicMin chains, largest index; emission over
+// the aliased sequence), but the atomics are shared-memory atomics and nothing is cleared or re-read through L2.  Used when
+// several lanes run at once (every lane gets an SM of its own) and the table fits.
+constexpr int kFusedThreads = 1024;
+
+__global__ void __launch_bounds__(kFusedThreads) bucket_lane_kernel(const float2* __restrict__ in_xy, const int* __restrict__ in_age,
+                                                                    size_t in_lane, const int* __restrict__ n_dev, int n_max,
+                                                                    int Wc, int nb, int bs, int k, BucketBufs bb)
+{
+    extern __shared__ int sm[];
+    int* cnt = sm;               // [nb]
+    int* last = sm + nb;         // [nb]
+    int* slots = sm + 2 * nb;    // [nb * k]
+    __shared__ int wsum[kFusedThreads / 32];
+    __shared__ int s_err;
+    const int lane_id = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, ln = tid & 31;
+    const int n = min(n_dev[lane_id], n_max);
+    const float2* ixy = in_xy + (size_t)lane_id * in_lane;
+
+    for (int i = tid; i < nb; i += kFusedThreads) { cnt[i] = 0; last[i] = -1; }
+    for (int i = tid; i < nb * k; i += kFusedThreads) slots[i] = kEmpty;
+    if (tid == 0) s_err = 0;
+    __syncthreads();
+
+    const float fbs = (float)bs;
+    float2 pnext = tid < n ? ixy[tid] : make_float2(0.f, 0.f);
+    for (int i = tid; i < n; i += kFusedThreads) {
+        const float2 p = pnext;
+        if (i + kFusedThreads < n) pnext = ixy[i + kFusedThreads];        // in flight while this point is inserted
+        const float fy = __fdiv_rn(p.y, fbs), fx = __fdiv_rn(p.x, fbs);   // float / int -> float, src/bucket.cpp:50-51
+        if (!(fabsf(fy) < 2.0e9f) || !(fabsf(fx) < 2.0e9f)) { s_err = 1; continue; }
+        const long long idx = (long long)(int)fy * Wc + (int)fx;           // truncation toward zero, stride Wc (:52)
+        if (idx < 0 || idx >= nb) { s_err = 1; continue; }                  // out-of-bounds write in the reference (UB)
+        atomicAdd(cnt + idx, 1);
+        atomicMax(last + idx, i);
+        int* s = slots + idx * k;
+        if (*reinterpret_cast<volatile int*>(s + k - 1) < i) continue;     // k smaller indices are already in
+        int v = i;
+        for (int j = 0; j < k; ++j) {
+            const int old = atomicMin(s + j, v);
+            if (old == kEmpty) break;
+            if (old > v) v = old;
+        }
+    }
+    __syncthreads();
+    if (tid == 0) bb.err_flag[lane_id] = s_err;
+
+    // emission: entry e of the (Hc+1) x (Wc+1) sequence reads bucket hh * Wc + ww (aliased buckets come out twice)
+    const int nemit = nb;
+    const int* iag = in_age ? in_age + (size_t)lane_id * in_lane : nullptr;
+    float2* oxy = bb.out_xy + (size_t)lane_id * bb.out_cap;
+    int* oag = bb.out_age + (size_t)lane_id * bb.out_cap;
+    int base = 0;
+    for (int e0 = 0; e0 < nemit; e0 += kFusedThreads) {
+        const int e = e0 + tid;
+        int idx = 0, m = 0;
+        if (e < nemit) {
+            const int hh = e / (Wc + 1), ww = e - hh * (Wc + 1);
+            idx = hh * Wc + ww;
+            m = min(cnt[idx], k);
+        }
+        int inc = m;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, inc, o);
+            if (ln >= o) inc += v;
+        }
+        if (ln == 31) wsum[warp] = inc;
+        __syncthreads();
+        int woff = 0, tot = 0;
+        for (int i = 0; i < kFusedThreads / 32; ++i) {
+            const int v = wsum[i];
+            if (i < warp) woff += v;
+            tot += v;
+        }
+        const int off = base + woff + inc - m;
+        if (m > 0) {
+            const bool overflow = cnt[idx] > k;
+            for (int s = 0; s < m; ++s) {
+                const int src = (s == 0 && overflow) ? last[idx] : slots[idx * k + s];
+                const int o = off + s;
+                if (o < bb.out_cap) {
+                    oxy[o] = ixy[src];
+                    oag[o] = iag ? iag[src] : 0;
+                }
+            }
+        }
+        base += tot;
+        __syncthreads();   // wsum is rewritten by the next chunk
+    }
+    if (tid == 0) bb.out_count[lane_id] = base;   // required output length (may exceed out_cap)
+}
+
 }  // namespace
 
 void launch_bucket(cudaStream_t st, const float2* in_xy, const int* in_age, size_t in_lane, const int* n_dev, int n_max,
@@ -154,9 +248,22 @@ void launch_bucket(cudaStream_t st, const float2* in_xy, const int* in_age, size
     const int nb = (Hc + 1) * (Wc + 1);
     const int k = per_bucket;
     static bool once = false;
+    static int smem_max = 0;
     if (!once) {
         prefer_max_shared(bucket_insert_kernel); prefer_max_shared(bucket_emit_kernel); prefer_max_shared(bucket_clear_kernel);
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+        smem_max -= 1024;   // the kernel's static shared memory
+        cudaFuncSetAttribute(bucket_lane_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max);
         once = true;
+    }
+    // several lanes at once and a table that fits in shared memory: one CTA per lane does the whole call
+    const size_t table = sizeof(int) * (size_t)nb * (size_t)(2 + k);
+    if (bb.mode != 1 && table <= (size_t)smem_max && (batch >= 4 || bb.mode == 2)) {
+        bucket_lane_kernel<<<batch, kFusedThreads, table, st>>>(in_xy, in_age, in_lane, n_dev, n_max, Wc, nb, bucket_size, k, bb);
+        if (launches) ++*launches;
+        return;
     }
     // whole-batch clear (lanes are contiguous), one launch
     {

@@ -280,6 +280,7 @@ static int create_buffers(svo_gpu_ctx* ctx)
     CK(cudaStreamCreateWithFlags(&ctx->aux_st, cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
+    if (const char* v = getenv("SVO_GPU_BUCKET_MODE")) ctx->bb.mode = atoi(v);   // 1: global-memory kernels, 2: one CTA per lane
     if (const char* v = getenv("SVO_GPU_STEP_OVERLAP")) ctx->overlap = atoi(v);
     if (const char* v = getenv("SVO_GPU_KLT_RESERVE")) ctx->klt_reserve = atoi(v);
     if (const char* v = getenv("SVO_GPU_FAST_SMALL")) ctx->fast_small = atoi(v);

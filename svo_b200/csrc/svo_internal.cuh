@@ -93,6 +93,7 @@ struct BucketBufs {
     int* out_age;         // [B][out_cap]
     int* out_count;       // [B]  required output count (may exceed out_cap)
     int out_cap;
+    int mode;             // 0: pick per call, 1: always the three global-memory kernels, 2: the one-CTA-per-lane kernel whenever its table fits
 };
 
 // in_xy: [B][in_lane] float2; in_age may be nullptr (all ages 0, FeatureSet::appendNewFeatures, src/bucket.cpp:18-22);
