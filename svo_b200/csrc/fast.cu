@@ -125,6 +125,8 @@ __global__ void __launch_bounds__(NT) fast_tile_kernel(const uint8_t* __restrict
 
     // ---- pass 1: dense packed corner score of every 4-pixel group of the score region (rows y0-1 .. y0+TH, staged
     //      columns 0 .. RW-1): sbest byte = max(best - t, 0), where best = cornerScore + 1.
+    // does the score region (x0-4 .. x0+TW+3, y0-1 .. y0+TH) reach into the 3-px frame?  (CTA-uniform)
+    const bool edge_tile = x0 - 4 < 3 || x0 + TW + 3 > w - 4 || y0 - 1 < 3 || y0 + TH > h - 4;
     const uint32_t bias = 0x01000100u;
     const uint32_t tt = (uint32_t)t * 0x00010001u;
     for (int idx = tid; idx < SH * NG; idx += NT) {
@@ -162,13 +164,15 @@ __global__ void __launch_bounds__(NT) fast_tile_kernel(const uint8_t* __restrict
         const uint32_t se = pmax(packed_best(De), floor_) - floor_;   // best - t, 0 if not a corner
         const uint32_t so = pmax(packed_best(Do), floor_) - floor_;
         uint32_t out = __byte_perm(se, so, 0x6240);                   // bytes: pixel 0, 1, 2, 3
-        // pixels outside the 3-px frame of the image are not candidates
-        const int gy = y0 - 1 + r, gx = x0 - 4 + 4 * g;
-        if (gy < 3 || gy > h - 4) out = 0;
-        else if (gx < 3 || gx + 3 > w - 4) {
+        // pixels outside the 3-px frame of the image are not candidates (only tiles at the image edge hold any)
+        if (edge_tile) {
+            const int gy = y0 - 1 + r, gx = x0 - 4 + 4 * g;
+            if (gy < 3 || gy > h - 4) out = 0;
+            else if (gx < 3 || gx + 3 > w - 4) {
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
-                if (gx + i < 3 || gx + i > w - 4) out &= ~(0xffu << (8 * i));
+                for (int i = 0; i < 4; ++i)
+                    if (gx + i < 3 || gx + i > w - 4) out &= ~(0xffu << (8 * i));
+            }
         }
         sbest[r * RWW + g] = out;
     }
@@ -214,11 +218,12 @@ __global__ void __launch_bounds__(NT) fast_tile_kernel(const uint8_t* __restrict
         const uint32_t b2 = __ballot_sync(0xffffffffu, bits & 4u), b3 = __ballot_sync(0xffffffffu, bits & 8u);
         const int total = __popc(b0) + __popc(b1) + __popc(b2) + __popc(b3);
         const size_t seg = (size_t)lane_id * seg_lane + (size_t)gy * ntx + blockIdx.x;
-        if (bits) {
+        if (bits) {   // mostly one keypoint per group: walk the set bits instead of testing all four
             uint16_t* out = fb.segkp + seg * TW + __popc(b0 & lt) + __popc(b1 & lt) + __popc(b2 & lt) + __popc(b3 & lt);
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-                if (bits >> i & 1u) *out++ = (uint16_t)((4 * ln + i) | (((wc >> (8 * i)) & 0xffu) << 8));
+            for (uint32_t rest = bits; rest; rest &= rest - 1u) {
+                const int i = __ffs((int)rest) - 1;
+                *out++ = (uint16_t)((4 * ln + i) | (((wc >> (8 * i)) & 0xffu) << 8));
+            }
         }
         if (ln == 0) {
             fb.segcnt[seg] = (uint8_t)total;
