@@ -247,16 +247,14 @@ void launch_bucket(cudaStream_t st, const float2* in_xy, const int* in_age, size
     const int Hc = img_h / bucket_size, Wc = img_w / bucket_size;
     const int nb = (Hc + 1) * (Wc + 1);
     const int k = per_bucket;
-    static bool once = false;
-    static int smem_max = 0;
-    if (!once) {
+    static std::atomic<unsigned long long> seen{0};
+    int dev = 0, smem_max = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    smem_max -= 1024;   // the kernel's static shared memory
+    if (first_on_device(seen)) {
         prefer_max_shared(bucket_insert_kernel); prefer_max_shared(bucket_emit_kernel); prefer_max_shared(bucket_clear_kernel);
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
-        smem_max -= 1024;   // the kernel's static shared memory
         cudaFuncSetAttribute(bucket_lane_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max);
-        once = true;
     }
     // several lanes at once and a table that fits in shared memory: one CTA per lane does the whole call
     const size_t table = sizeof(int) * (size_t)nb * (size_t)(2 + k);

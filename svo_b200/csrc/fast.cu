@@ -320,10 +320,9 @@ void launch_fast(cudaStream_t st, const uint8_t* raw, size_t raw_pitch, size_t r
         cudaMemsetAsync(fb.kp_count, 0, sizeof(int) * batch, st);
         return;
     }
-    static bool once = false;
-    if (!once) {
+    static std::atomic<unsigned long long> seen{0};
+    if (first_on_device(seen)) {
         prefer_max_shared(fast_tile_kernel<128>); prefer_max_shared(fast_tile_kernel<256>); prefer_max_shared(fast_gather_kernel);
-        once = true;
     }
     const int ntx = (w + TW - 1) / TW;
     dim3 grid(ntx, (h + TH - 1) / TH, batch);
@@ -344,8 +343,8 @@ void launch_build_mask(cudaStream_t st, uint8_t* mask, size_t mask_pitch, size_t
     // one fill for all lanes (lanes are mask_lane apart and the padding of a lane is never read)
     cudaMemsetAsync(mask, 255, (size_t)(batch - 1) * mask_lane + (size_t)(h - 1) * mask_pitch + (size_t)w, st);
     if (n_max <= 0) return;
-    static bool once = false;
-    if (!once) { prefer_max_shared(mask_boxes_kernel); once = true; }
+    static std::atomic<unsigned long long> seen{0};
+    if (first_on_device(seen)) prefer_max_shared(mask_boxes_kernel);
     mask_boxes_kernel<<<dim3((n_max + 3) / 4, batch), 128, 0, st>>>(mask, mask_pitch, mask_lane, w, h, pts, pts_lane,
                                                                   n_dev, n_max, half);
     if (launches) ++*launches;

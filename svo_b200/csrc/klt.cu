@@ -603,15 +603,12 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) klt_run_kernel(const KltArgs
 template <int WW, int WH, int WARPS, bool PACKG, int MINB>
 bool launch_run(cudaStream_t st, const KltArgs& a, int batch, int part, int reserve)
 {
-    static int sms = 0;
-    if (!sms) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        // every kernel that may share an SM with this one asks for the same (largest) shared-memory carve-out
-        cudaFuncSetAttribute(klt_run_kernel<WW, WH, WARPS, PACKG, MINB>, cudaFuncAttributePreferredSharedMemoryCarveout,
-                             cudaSharedmemCarveoutMaxShared);
-    }
+    static std::atomic<unsigned long long> seen{0};
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    // every kernel that may share an SM with this one asks for the same (largest) shared-memory carve-out
+    if (first_on_device(seen)) prefer_max_shared(klt_run_kernel<WW, WH, WARPS, PACKG, MINB>);
     reserve = std::max(0, std::min(reserve, MINB - 1));
     const int per_sm = part == kKltAll ? MINB : part == kKltMain ? MINB - reserve : reserve;
     if (per_sm <= 0) return false;

@@ -9,6 +9,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
+
 #include "svo_gpu.h"
 
 namespace svo {
@@ -28,6 +30,16 @@ struct PyrGeom {
     LevelGeom lv[kMaxLevels];
     long long lane_bytes;   // stride between lanes
 };
+
+// Function attributes (carve-out, dynamic shared-memory limit) are per device: true the first time a launch site runs on
+// the calling thread's current device (one host thread per GPU may share this library).
+inline bool first_on_device(std::atomic<unsigned long long>& seen)
+{
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const unsigned long long bit = 1ull << (dev & 63);
+    return (seen.fetch_or(bit) & bit) == 0;
+}
 
 // Kernels that may share an SM with the persistent LK kernel (the step runs FAST and bucketing beside it) all ask for
 // the same, largest shared-memory carve-out: CTAs of kernels with different carve-outs cannot be co-resident on an SM.
