@@ -371,6 +371,14 @@ def run_b200(args):
                   "status_ok_frac": ok_sum / max(trk_sum, 1)},
     }
     line["klt_tracks_per_s"] = world * S * n_trk * K / (dev_ms * 1e-3)
+    # stage-only rates (KLT-only and FAST-only reported next to the whole front-end), this rank's launches
+    line["stage_rates"] = {
+        "klt_only_tracks_per_s": S * n_trk / (klt["ms"] * 1e-3) if klt["ms"] > 0 else None,
+        "fast_only_frames_per_s": S / (kernels["fast"]["ms"] * 1e-3) if kernels["fast"]["ms"] > 0 else None,
+        "pyramid_only_frames_per_s": S / (kernels["pyramid"]["ms"] * 1e-3) if kernels["pyramid"]["ms"] > 0 else None,
+        "bucket_only_frames_per_s": S / (kernels["bucket"]["ms"] * 1e-3) if kernels["bucket"]["ms"] > 0 else None,
+        "note": "per GPU; stage time = CUDA events around the stage's launches inside the timed region",
+    }
     line["config"]["pipelining"] = "svo_gpu_step_submit / _wait, 2 steps outstanding; every step's results are waited for"
     # the bound LK actually runs against: warp instructions issued per second.  Instructions per launch come from the ncu
     # capture of this same workload (profiles/ncu_traffic.json, 64 x 2000 tracks), the launch time is measured here.
