@@ -277,7 +277,11 @@ static int create_buffers(svo_gpu_ctx* ctx)
     CK(cudaStreamCreateWithFlags(&ctx->out_st, cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&ctx->ev_klt, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&ctx->ev_out, cudaEventDisableTiming));
-    CK(cudaStreamCreateWithFlags(&ctx->aux_st, cudaStreamNonBlocking));
+    {   // lowest priority: detection CTAs only take what the LK kernel (on st, default priority) leaves free
+        int lo = 0, hi = 0;
+        CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        CK(cudaStreamCreateWithPriority(&ctx->aux_st, cudaStreamNonBlocking, lo));
+    }
     CK(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
     if (const char* v = getenv("SVO_GPU_BUCKET_MODE")) ctx->bb.mode = atoi(v);   // 1: global-memory kernels, 2: one CTA per lane
