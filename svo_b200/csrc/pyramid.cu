@@ -18,16 +18,20 @@ namespace svo {
 // ingest_kernel: five aligned words + four funnel shifts, rows of any pitch / alignment (compact uploads have pitch = w).
 // The few chunks per row that touch the left / right margin go to ingest_edge_kernel, whose warps hold 32 consecutive ROWS
 // of one edge chunk, so that the per-byte BORDER_REFLECT_101 path never shares a warp with the streaming path.
-// grid = (ceil(nfast / 128), h+2P, batch)  and  (ceil((h+2P) / 128), nedge, batch)
+// grid = (ceil(nfast (h+2P) / 256), 1, batch): (row, chunk) pairs flattened, so that every thread of a CTA has a chunk whatever
+// the row length  and  (ceil((h+2P) / 128), nedge, batch)
 // ---------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) ingest_kernel(const uint8_t* __restrict__ raw, size_t raw_pitch, size_t raw_lane,
+__global__ void __launch_bounds__(256) ingest_kernel(const uint8_t* __restrict__ raw, size_t raw_pitch, size_t raw_lane,
                                                      uint8_t* __restrict__ pyr, long long lane_bytes, LevelGeom L, int P,
                                                      int c_begin, int c_end)
 {
-    const int c = c_begin + blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= c_end) return;
+    const int nfast = c_end - c_begin;
+    const int item = blockIdx.x * blockDim.x + threadIdx.x;
+    const int row = item / nfast;
+    if (row >= L.h + 2 * P) return;
+    const int c = c_begin + (item - row * nfast);
     const int x0 = 16 * c - P;
-    const int py = (int)blockIdx.y - P;
+    const int py = row - P;
     const int lane = blockIdx.z;
     const uint8_t* srow = raw + (size_t)lane * raw_lane + (size_t)reflect101(py, L.h) * raw_pitch;
     const uintptr_t addr = reinterpret_cast<uintptr_t>(srow + x0);
@@ -78,7 +82,7 @@ __global__ void __launch_bounds__(128) ingest_edge_kernel(const uint8_t* __restr
 //   out0 = w0 . (0,0,1,4)K + w1 . (6,4,1,0)K     out1 = w1 . (1,4,6,4)K + w2 . (1,0,0,0)K
 //   out2 = w1 . (0,0,1,4)K + w2 . (6,4,1,0)K     out3 = w2 . (1,4,6,4)K + w3 . (1,0,0,0)K      (K = 1, 4, 6, 4, 1 per row)
 // i.e. 8 DP4A per source row and no shifts or byte extraction.
-// grid = (ceil(ceil(dw/4) / 128), dh, batch)
+// grid = (ceil(ceil(dw/4) dh / 256), 1, batch)
 // ---------------------------------------------------------------------------------------------------------------
 // smallest value >= lo that is congruent to v modulo period
 __device__ __forceinline__ int first_at_least(int v, int period, int lo)
@@ -93,12 +97,14 @@ __device__ __forceinline__ uint32_t pack4(uint32_t a, uint32_t b, uint32_t c, ui
     return a | (b << 8) | (c << 16) | (d << 24);
 }
 
-__global__ void __launch_bounds__(128) pyrdown_kernel(uint8_t* __restrict__ pyr, long long lane_bytes, LevelGeom S,
-                                                      LevelGeom D, int P)
+__global__ void __launch_bounds__(256) pyrdown_kernel(uint8_t* __restrict__ pyr, long long lane_bytes, LevelGeom S,
+                                                      LevelGeom D, int P, int quads)
 {
-    const int px = 4 * (blockIdx.x * blockDim.x + threadIdx.x);
-    if (px >= D.w) return;
-    const int py = blockIdx.y;
+    // (row, quad) pairs flattened: every thread of a CTA has work whatever the row length
+    const int item = blockIdx.x * blockDim.x + threadIdx.x;
+    const int py = item / quads;
+    if (py >= D.h) return;
+    const int px = 4 * (item - py * quads);
     uint8_t* base = pyr + (size_t)blockIdx.z * lane_bytes;
     // source columns 2px-4 .. 2px+11 (bytes 2..12 are used), rows 2py-2 .. 2py+2; 2px-4 is 4 mod 8: one 32-bit, one 64-bit,
     // one 32-bit load per row
@@ -179,8 +185,8 @@ void launch_ingest(cudaStream_t st, const uint8_t* raw, size_t raw_pitch, size_t
     const int c_end = L.w >= 20 ? std::max(c_begin, (L.w - 20 + P) / 16 + 1) : c_begin;
     const int rows = L.h + 2 * P;
     if (c_end > c_begin) {
-        dim3 grid((c_end - c_begin + 127) / 128, rows, batch);
-        ingest_kernel<<<grid, 128, 0, st>>>(raw, raw_pitch, raw_lane, pyr, g.lane_bytes, L, P, c_begin, c_end);
+        dim3 grid(((c_end - c_begin) * rows + 255) / 256, 1, batch);
+        ingest_kernel<<<grid, 256, 0, st>>>(raw, raw_pitch, raw_lane, pyr, g.lane_bytes, L, P, c_begin, c_end);
         if (launches) ++*launches;
     }
     const int n_edge = c_begin + (n_chunks - c_end);
@@ -240,8 +246,8 @@ void launch_pyrdown(cudaStream_t st, uint8_t* pyr, const PyrGeom& g, int level, 
     const LevelGeom& S = g.lv[level - 1];
     const LevelGeom& D = g.lv[level];
     const int quads = (D.w + 3) / 4;
-    dim3 grid((quads + 127) / 128, D.h, batch);
-    pyrdown_kernel<<<grid, 128, 0, st>>>(pyr, g.lane_bytes, S, D, g.P);
+    dim3 grid((quads * D.h + 255) / 256, 1, batch);
+    pyrdown_kernel<<<grid, 256, 0, st>>>(pyr, g.lane_bytes, S, D, g.P, quads);
     if (launches) ++*launches;
 }
 
