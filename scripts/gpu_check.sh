@@ -17,6 +17,6 @@ timeout 600 $SHORT > $OUT/plain.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $OUT/launches.csv $SHORT > $OUT/ncu_launch.log 2>&1
 echo "ncu launches rc=$?"
 timeout 600 $SHORT > $OUT/plain2.log 2>&1 &&
-timeout 1500 ncu --set full --clock-control none --import-source on -k 'regex:klt_|fast_|pyrdown|ingest|bucket_|seed_tracks|mask_boxes' -s 60 -c 11 -o $OUT/prof $SHORT > $OUT/ncu_full.log 2>&1
+timeout 1500 ncu --set full --clock-control none --import-source on -k 'regex:klt_|fast_|pyrdown|ingest|bucket_|seed_tracks|mask_boxes' -s 65 -c 12 -o $OUT/prof $SHORT > $OUT/ncu_full.log 2>&1
 echo "ncu full rc=$?"
 ls -la $OUT
