@@ -72,6 +72,12 @@ SVO_GPU_API void* svo_gpu_stream(svo_gpu_ctx* ctx);
 /* ABI version of this header */
 SVO_GPU_API int svo_gpu_abi_version(void);
 
+/* Page-locked host memory for frames and result arrays that should move while kernels run (cudaMemcpyAsync only overlaps
+ * from pinned memory).  Plays the part of the cv::Mat buffers the reference's loader thread fills ahead of time
+ * (include/async_image_loader.h:27-33).  Not tied to a context; free with svo_gpu_host_free. */
+SVO_GPU_API int svo_gpu_host_alloc(void** out, size_t bytes);
+SVO_GPU_API int svo_gpu_host_free(void* p);
+
 /* ---------------------------------------------------------------------------------------------- images -------- */
 
 /* Copies one 8-bit gray image (cv::Mat CV_8UC1: data, cols, rows, step) into `slot`, lane 0.

@@ -29,6 +29,8 @@ SYMBOLS = {
     "svo_gpu_last_error": (C.c_char_p, [C.c_void_p]),
     "svo_gpu_stream": (C.c_void_p, [C.c_void_p]),
     "svo_gpu_abi_version": (C.c_int, []),
+    "svo_gpu_host_alloc": (C.c_int, [C.POINTER(C.c_void_p), C.c_size_t]),
+    "svo_gpu_host_free": (C.c_int, [C.c_void_p]),
     "svo_gpu_upload": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_size_t]),
     "svo_gpu_upload_batch": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_size_t,
                                        C.c_size_t, C.c_int]),

@@ -365,6 +365,22 @@ extern "C" int svo_gpu_destroy(svo_gpu_ctx* ctx)
     return 0;
 }
 
+extern "C" int svo_gpu_host_alloc(void** out, size_t bytes)
+{
+    svo_gpu_ctx* ctx = nullptr;   // failures are reported like those of svo_gpu_create
+    if (!out || bytes == 0) return fail(ctx, SVO_GPU_E_ARG, "svo_gpu_host_alloc: null pointer or zero size");
+    *out = nullptr;
+    CK(cudaMallocHost(out, bytes));
+    return 0;
+}
+
+extern "C" int svo_gpu_host_free(void* p)
+{
+    svo_gpu_ctx* ctx = nullptr;
+    if (p) CK(cudaFreeHost(p));
+    return 0;
+}
+
 // ================================================================================================ images
 // copies `batch` images into the slot on stream `cs` (enqueue only).  Host images that are tightly packed (stride == w,
 // images back to back) go over PCIe as ONE contiguous copy and stay compact on the device (row pitch w: the ingest kernel

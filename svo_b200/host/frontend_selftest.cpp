@@ -11,6 +11,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 
 #include "bucket.h"
 
@@ -40,6 +41,57 @@ int main(int argc, char** argv)
         }
         fprintf(stderr, "detect() returned without a GPU: a CPU fallback must not exist\n");
         return 1;
+    }
+    if (argc == 4 && !strcmp(argv[1], "--batch")) {
+        // svo::SequenceBatch the way a many-sequence driver uses it: frame set t + 1 is submitted before set t is waited for.
+        // in.bin = int32 {w, h, streams, frames, max_tracks}, then frames x streams images; out.bin = per frame, per stream:
+        // n_tracked, tracked xy, status, err, n_features, features xy, keypoints
+        FILE* fi = fopen(argv[2], "rb");
+        if (!fi) return 2;
+        int hdr[5];
+        if (fread(hdr, sizeof(int), 5, fi) != 5) return 2;
+        const int w = hdr[0], h = hdr[1], S = hdr[2], T = hdr[3];
+        std::vector<std::vector<cv::Mat>> seq((size_t)T, std::vector<cv::Mat>((size_t)S));
+        for (auto& fs : seq)
+            for (auto& m : fs) {
+                m.create(h, w, CV_8UC1);
+                if (fread(m.data, 1, (size_t)w * h, fi) != (size_t)w * h) return 2;
+            }
+        fclose(fi);
+        FILE* fo = fopen(argv[3], "wb");
+        try {
+            svo::FrontendParams fp;
+            fp.maxTracks = hdr[4];
+            svo::SequenceBatch batch(0, w, h, S, fp);
+            std::vector<svo::SequenceResult> res;
+            auto dump = [&]() {
+                batch.wait(res);
+                for (const auto& r : res) {
+                    put_i(fo, (int)r.tracked.size());
+                    put(fo, r.tracked.data(), 8 * r.tracked.size());
+                    put(fo, r.status.data(), r.status.size());
+                    put(fo, r.err.data(), 4 * r.err.size());
+                    put_i(fo, (int)r.features.size());
+                    put(fo, r.features.data(), 8 * r.features.size());
+                    put_i(fo, r.keypoints);
+                }
+            };
+            batch.submit(seq[0]);
+            for (int t = 1; t < T; ++t) {
+                batch.submit(seq[(size_t)t]);
+                dump();   // frame set t - 1, while set t runs
+            }
+            dump();
+            bool threw = false;
+            try { batch.wait(res); } catch (const cv::Exception&) { threw = true; }   // nothing outstanding
+            put_i(fo, threw ? 1 : 0);
+        } catch (const cv::Exception& e) {
+            fprintf(stderr, "frontend_selftest --batch: %s\n", e.what());
+            fclose(fo);
+            return 1;
+        }
+        fclose(fo);
+        return 0;
     }
     if (argc != 3) return 2;
     FILE* fi = fopen(argv[1], "rb");

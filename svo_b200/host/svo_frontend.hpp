@@ -103,6 +103,57 @@ void extractStereoFeatures(const cv::Mat& leftImg, const cv::Mat& rightImg, cons
                            int threshold, bool nms, float yThreshold, std::vector<cv::Point2f>& leftPts,
                            std::vector<cv::Point2f>& rightPts, int bucketSize = 0, int featuresPerBucket = 0);
 
+// ---- many independent sequences on one GPU (BASELINE config 5) --------------------------------------------
+// The loop body of Tracking::startStereo (src/tracking.cpp:240-257) for `streams` sequences at once: per sequence, LK
+// (trackFrames, :154-179) from its previous frame on its current tracks, then FAST around a mask of those tracks and
+// bucketing (extractFeatures, :74-92); the first maxTracks bucketed detections become the sequence's tracks for the next
+// frame.  One object = one device context; sequences never interact.  Frames are submitted and waited for separately,
+// with up to two frame sets outstanding, so that the host (pose estimation, mapping) works on frame t while the GPU
+// already runs frame t + 1 -- the overlap the reference gets from its loader thread (include/async_image_loader.h:27-33).
+struct FrontendParams {
+    int fastThreshold = 20;           // include/config_reader.h:36
+    bool nonmaxSuppression = true;    // include/config_reader.h:37
+    float maskHalf = 10.f;            // src/tracking.cpp:78; <= 0: no mask
+    int bucketSize = 32, featuresPerBucket = 5;
+    int maxTracks = 2000;
+    cv::Size winSize = cv::Size(21, 21);   // src/tracking.cpp:163
+    int maxLevel = 3;
+    cv::TermCriteria criteria = cv::TermCriteria(cv::TermCriteria::COUNT + cv::TermCriteria::EPS, 50, 0.001);   // :157
+    int flags = cv::OPTFLOW_LK_GET_MIN_EIGENVALS;                                                              // :164
+    double minEigThreshold = 1e-4;
+};
+
+struct SequenceResult {
+    std::vector<cv::Point2f> tracked;   // LK result for each track carried into this frame (empty on a sequence's first frame)
+    std::vector<uchar> status;
+    std::vector<float> err;
+    std::vector<cv::Point2f> features;  // bucketed detections of this frame; the first maxTracks are the next frame's tracks
+    int keypoints = 0;                  // FAST keypoints found before bucketing
+};
+
+class SequenceBatch {
+public:
+    SequenceBatch(int device, int width, int height, int streams, const FrontendParams& params = FrontendParams());
+    ~SequenceBatch();
+    SequenceBatch(const SequenceBatch&) = delete;
+    SequenceBatch& operator=(const SequenceBatch&) = delete;
+
+    // One CV_8UC1 frame of the configured size per sequence.  Copies them to page-locked staging and enqueues the step.
+    void submit(const std::vector<cv::Mat>& frames);
+    // Waits for the oldest outstanding frame set; results[s] belongs to sequence s.
+    void wait(std::vector<SequenceResult>& results);
+    int outstanding() const { return submitted_ - waited_; }
+    void reset();   // forget every sequence's previous frame and tracks
+
+private:
+    struct Set;
+    svo_gpu_ctx* ctx_ = nullptr;
+    int w_, h_, streams_, bucket_cap_;
+    FrontendParams p_;
+    Set* sets_[SVO_GPU_STEP_DEPTH] = {};
+    int submitted_ = 0, waited_ = 0;
+};
+
 // The filter loop alone (src/tracking.cpp:109-115; yThreshold < 0: :168-175) for callers that ran LK themselves.
 void filterTracks(const std::vector<cv::Point2f>& a, const std::vector<cv::Point2f>& b, const std::vector<uchar>& status,
                   float yThreshold, std::vector<int>& indices);

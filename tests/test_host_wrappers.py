@@ -44,6 +44,45 @@ def test_reference_signatures_declared():
 
 
 @pytest.mark.gpu
+def test_sequence_batch_matches_cpu_pipeline(exe, oracle, tmp_path):
+    """svo::SequenceBatch (C++ driver of svo_gpu_step_submit / _wait, two frame sets outstanding) against the CPU pipeline
+    built from the oracle, per sequence and per frame, bit-exact."""
+    from oracle.cpu_pipeline import CpuFrontend
+    from svo_b200.frontend import make_params
+    w, h, S, T, max_tracks = 320, 240, 3, 5, 400
+    seqs = np.stack([synth.sequence(w, h, seed, T) for seed in (5, 6, 7)])      # [stream, t, h, w]
+    fin, fout = tmp_path / "bin.bin", tmp_path / "bout.bin"
+    with open(fin, "wb") as f:
+        np.array([w, h, S, T, max_tracks], np.int32).tofile(f)
+        np.ascontiguousarray(seqs.transpose(1, 0, 2, 3)).tofile(f)
+    r = subprocess.run([exe, "--batch", str(fin), str(fout)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    buf = open(fout, "rb").read()
+    off = 0
+
+    def take(dtype, n):
+        nonlocal off
+        out = np.frombuffer(buf, dtype, n, off)
+        off += out.nbytes
+        return out
+
+    _, pdict = make_params(w, h, max_tracks=max_tracks, mask_half=10.0)          # svo::FrontendParams defaults
+    cpus = [CpuFrontend(pdict, impl="orc") for _ in range(S)]
+    for t in range(T):
+        for s in range(S):
+            ref = cpus[s].step(seqs[s, t])
+            nt = int(take(np.int32, 1)[0])
+            xy, st, er = take(np.float32, 2 * nt).reshape(nt, 2), take(np.uint8, nt), take(np.float32, nt)
+            nb = int(take(np.int32, 1)[0])
+            feats = take(np.float32, 2 * nb).reshape(nb, 2)
+            nk = int(take(np.int32, 1)[0])
+            assert nt == len(ref["next_xy"]) and (t == 0 or nt > 100), (t, s)
+            assert np.array_equal(xy, ref["next_xy"]) and np.array_equal(st, ref["status"]) and np.array_equal(er, ref["err"]), (t, s)
+            assert nk == len(ref["kp_xy"]) and np.array_equal(feats, ref["bucket_xy"]), (t, s)
+    assert int(take(np.int32, 1)[0]) == 1 and off == len(buf)
+
+
+@pytest.mark.gpu
 def test_wrappers_match_oracle(exe, oracle, tmp_path):
     w, h, bs, k = 320, 240, 32, 5
     canvas = synth.make_canvas(w, h, 5)
