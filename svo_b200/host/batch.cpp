@@ -97,6 +97,14 @@ void SequenceBatch::submit(const std::vector<cv::Mat>& frames)
         uint8_t* dst = s.frames + (size_t)b * w_ * h_;
         for (int y = 0; y < h_; ++y) memcpy(dst + (size_t)y * w_, m.data + (size_t)y * m.step, (size_t)w_);
     }
+    submit(s.frames);
+}
+
+void SequenceBatch::submit(const uint8_t* frames)
+{
+    if (!frames) throw cv::Exception("SequenceBatch::submit: frames is null");
+    if (outstanding() >= SVO_GPU_STEP_DEPTH) throw cv::Exception("SequenceBatch::submit: wait for the oldest frame set first");
+    Set& s = *sets_[submitted_ % SVO_GPU_STEP_DEPTH];
     svo_gpu_step_params P{};
     P.w = w_; P.h = h_;
     P.fast_threshold = p_.fastThreshold; P.fast_nms = p_.nonmaxSuppression ? 1 : 0; P.mask_half = p_.maskHalf;
@@ -104,7 +112,7 @@ void SequenceBatch::submit(const std::vector<cv::Mat>& frames)
     P.win_w = p_.winSize.width; P.win_h = p_.winSize.height; P.max_level = p_.maxLevel;
     P.max_count = p_.criteria.maxCount; P.epsilon = p_.criteria.epsilon; P.criteria_type = p_.criteria.type;
     P.flags = p_.flags; P.min_eig_threshold = p_.minEigThreshold;
-    const int rc = svo_gpu_step_submit(ctx_, s.frames, nullptr, SVO_GPU_MEM_HOST, (size_t)w_, (size_t)w_ * h_, streams_, &P,
+    const int rc = svo_gpu_step_submit(ctx_, frames, nullptr, SVO_GPU_MEM_HOST, (size_t)w_, (size_t)w_ * h_, streams_, &P,
                                        &s.out, &s.ticket);
     if (rc != SVO_GPU_OK) raise(ctx_, "svo_gpu_step_submit", rc);
     ++submitted_;

@@ -140,6 +140,9 @@ public:
 
     // One CV_8UC1 frame of the configured size per sequence.  Copies them to page-locked staging and enqueues the step.
     void submit(const std::vector<cv::Mat>& frames);
+    // The same without the staging copy: `streams` images back to back with compact rows (width bytes each), in memory the
+    // caller keeps unchanged until the matching wait() -- page-locked (svo_gpu_host_alloc) if the copy is to overlap kernels.
+    void submit(const uint8_t* frames);
     // Waits for the oldest outstanding frame set; results[s] belongs to sequence s.
     void wait(std::vector<SequenceResult>& results);
     int outstanding() const { return submitted_ - waited_; }
