@@ -630,6 +630,15 @@ bool launch_run(cudaStream_t st, const KltArgs& a, int batch, int part, int rese
 #ifndef KLT21_MINB
 #define KLT21_MINB 20
 #endif
+#ifndef KLT11_MINB
+#define KLT11_MINB 32   // one run per lane, 64 registers: 16 -> 32 CTAs per SM, 0.757 -> 0.667 ms per 128 k tracks (gpurun_out: w11 sweep)
+#endif
+#ifndef KLT31_PACKG
+#define KLT31_PACKG true
+#endif
+#ifndef KLT31_MINB
+#define KLT31_MINB 12   // 3 warps per scheduler: 6.14 -> 5.64 ms on the 4K / 50 k-track workload (8 and 10 CTAs per SM measured equal)
+#endif
 
 }  // namespace
 
@@ -640,8 +649,8 @@ void launch_klt(cudaStream_t st, const KltArgs& a, int batch, long long* launche
     if (a.n_max <= 0) return;
     bool launched = true;
     if (a.win_w == 21 && a.win_h == 21) launched = launch_run<21, 21, KLT21_WARPS, KLT21_PACKG, KLT21_MINB>(st, a, batch, part, reserve);
-    else if (a.win_w == 11 && a.win_h == 11) launched = launch_run<11, 11, 1, false, 16>(st, a, batch, part, reserve);
-    else if (a.win_w == 31 && a.win_h == 31) launched = launch_run<31, 31, 1, true, 8>(st, a, batch, part, reserve);
+    else if (a.win_w == 11 && a.win_h == 11) launched = launch_run<11, 11, 1, false, KLT11_MINB>(st, a, batch, part, reserve);
+    else if (a.win_w == 31 && a.win_h == 31) launched = launch_run<31, 31, 1, KLT31_PACKG, KLT31_MINB>(st, a, batch, part, reserve);
     else if (part != kKltHelper) launch_klt_generic(st, a, batch);   // not persistent: the main launch is the whole job
     else launched = false;
     if (launches && launched) ++*launches;

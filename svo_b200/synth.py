@@ -17,6 +17,8 @@ WORKLOADS = {
     "C2": dict(w=752, h=480, n_tracks=5000, fast_thr=10, bucket_size=24, per_bucket=8, win=21, max_level=3, seed=12),
     "C3": dict(w=1920, h=1080, n_tracks=10000, fast_thr=20, bucket_size=32, per_bucket=5, win=21, max_level=4, seed=13),
     "C4": dict(w=3840, h=2160, n_tracks=50000, fast_thr=20, bucket_size=24, per_bucket=8, win=31, max_level=5, seed=14),
+    # C1 with the reference's stereo-matching window (src/tracking.cpp:104: 11x11): times the 11x11 LK instantiation
+    "C1w11": dict(w=1241, h=376, n_tracks=2000, fast_thr=20, bucket_size=32, per_bucket=5, win=11, max_level=3, seed=11),
 }
 
 
