@@ -108,7 +108,7 @@ struct svo_gpu_ctx {
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     int overlap = 0;        // SVO_GPU_STEP_OVERLAP (0 = one stream, stages back to back; 1 measured slower, gpurun_out/s6)
     int klt_reserve = 3;    // SVO_GPU_KLT_RESERVE
-    int fast_small = 1;     // SVO_GPU_FAST_SMALL: 128-thread FAST CTAs in the overlapped step
+    int fast_small = 1;     // SVO_GPU_FAST_SMALL: 128-thread FAST CTAs in the step (0 = 256)
     const uint8_t* pf_ptr = nullptr;   // host pointer of the prefetched frames (nullptr = none pending)
     int pf_slot = -1;
     float stage_ms[4] = {0, 0, 0, 0};

@@ -83,7 +83,7 @@ __device__ __forceinline__ uint32_t packed_best(const uint32_t (&D)[16])
 
 // scalar cornerScore<16> kept for reference in comments of the tests: see oracle/svo_oracle.c:orc_corner_score
 
-// NT threads per CTA (256, or 128 when the CTAs are meant to fit beside the persistent LK kernel: 8 192 registers each)
+// NT threads per CTA: 128 (8 192 registers per CTA, eight CTAs per SM) or 256
 template <int NT>
 __global__ void __launch_bounds__(NT) fast_tile_kernel(const uint8_t* __restrict__ raw, size_t raw_pitch, size_t raw_lane,
                                                        int w, int h, int t, int nms, const uint8_t* __restrict__ mask,
@@ -312,7 +312,7 @@ __global__ void __launch_bounds__(128) mask_boxes_kernel(uint8_t* __restrict__ m
 
 void launch_fast(cudaStream_t st, const uint8_t* raw, size_t raw_pitch, size_t raw_lane, int w, int h, int threshold,
                  int nms, const uint8_t* mask, size_t mask_pitch, size_t mask_lane, const FastBufs& fb, int batch,
-                 long long* launches, bool small_ctas)
+                 long long* launches, int small_ctas)
 {
     threshold = threshold < 0 ? 0 : (threshold > 255 ? 255 : threshold);
     cudaMemsetAsync(fb.rowtotal, 0, sizeof(int) * (size_t)fb.rows_cap * batch, st);
@@ -326,7 +326,7 @@ void launch_fast(cudaStream_t st, const uint8_t* raw, size_t raw_pitch, size_t r
     }
     const int ntx = (w + TW - 1) / TW;
     dim3 grid(ntx, (h + TH - 1) / TH, batch);
-    if (small_ctas)
+    if (small_ctas)   // the default: 128-thread CTAs measured 2 % faster than 256 (and 64 slower), gpurun_out/s11, s12
         fast_tile_kernel<128><<<grid, 128, 0, st>>>(raw, raw_pitch, raw_lane, w, h, threshold, nms, mask, mask_pitch, mask_lane,
                                                     fb, ntx);
     else

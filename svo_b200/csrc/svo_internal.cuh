@@ -86,7 +86,7 @@ struct FastBufs {
 // mask: device u8 plane per lane (pitch mask_pitch, lane stride mask_lane) or nullptr
 void launch_fast(cudaStream_t st, const uint8_t* raw, size_t raw_pitch, size_t raw_lane, int w, int h, int threshold,
                  int nms, const uint8_t* mask, size_t mask_pitch, size_t mask_lane, const FastBufs& fb, int batch,
-                 long long* launches, bool small_ctas = false);
+                 long long* launches, int small_ctas = 1);
 // mask plane = 255, then 0 in the rounded inclusive box around each point (src/tracking.cpp:76-79)
 // pts: [B][pts_lane] float2, n per lane from n_dev[lane] (device) clamped to n_max
 void launch_build_mask(cudaStream_t st, uint8_t* mask, size_t mask_pitch, size_t mask_lane, int w, int h,
