@@ -379,6 +379,9 @@ def run_b200(args):
         "bucket_only_frames_per_s": S / (kernels["bucket"]["ms"] * 1e-3) if kernels["bucket"]["ms"] > 0 else None,
         "note": "per GPU; stage time = CUDA events around the stage's launches inside the timed region",
     }
+    line["kernels"]["note"] = ("stage times are live CUDA-event brackets inside the timed region; the pyramid of step t+1 is "
+                               "built on a second stream beside FAST and bucketing of step t (SVO_GPU_STEP_PYR_ASYNC=1), so the "
+                               "pyramid and FAST brackets overlap each other and their sum exceeds ms_per_step; LK runs alone")
     line["config"]["pipelining"] = "svo_gpu_step_submit / _wait, 2 steps outstanding; every step's results are waited for"
     # the bound LK actually runs against: warp instructions issued per second.  Instructions per launch come from the ncu
     # capture of this same workload (profiles/ncu_traffic.json, 64 x 2000 tracks), the launch time is measured here.

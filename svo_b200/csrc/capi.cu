@@ -40,6 +40,7 @@ struct StepTicket {
     cudaEvent_t done = nullptr;
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t eva[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t evk = nullptr;    // main stream, in front of LK (the pyramid may have been built on another stream, earlier)
     svo_gpu_step_outputs out{};
     bool has_out = false, prof = false, track = false, overlap = false;
     int batch = 0, kp_cap = 0;
@@ -105,6 +106,11 @@ struct svo_gpu_ctx {
     // detection beside tracking: mask, FAST and bucketing run on aux_st while the LK kernel keeps klt_reserve CTA slots per
     // SM free for them; a helper launch of the LK kernel on aux_st takes those slots over afterwards (same work queue)
     cudaStream_t aux_st = nullptr;
+    // the step builds the new frame's pyramid on pyr_st (highest priority): with a step still in flight it runs beside that
+    // step's FAST and bucketing, as soon as that step's LK no longer needs the slot's previous pyramid
+    cudaStream_t pyr_st = nullptr;
+    cudaEvent_t ev_pyr = nullptr;
+    int pyr_async = 1;      // SVO_GPU_STEP_PYR_ASYNC (0 = pyramid on the main stream)
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     int overlap = 0;        // SVO_GPU_STEP_OVERLAP (0 = one stream, stages back to back; 1 measured slower, gpurun_out/s6)
     int klt_reserve = 3;    // SVO_GPU_KLT_RESERVE
@@ -270,6 +276,7 @@ static int create_buffers(svo_gpu_ctx* ctx)
         CK(cudaEventCreateWithFlags(&tk.done, cudaEventDisableTiming));
         for (auto& e : tk.ev) CK(cudaEventCreate(&e));
         for (auto& e : tk.eva) CK(cudaEventCreate(&e));
+        CK(cudaEventCreate(&tk.evk));
     }
     for (auto& e : ctx->ev_raw_free) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     CK(cudaStreamCreateWithFlags(&ctx->copy_st, cudaStreamNonBlocking));
@@ -284,6 +291,13 @@ static int create_buffers(svo_gpu_ctx* ctx)
     }
     CK(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
+    {
+        int lo = 0, hi = 0;
+        CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        CK(cudaStreamCreateWithPriority(&ctx->pyr_st, cudaStreamNonBlocking, hi));
+        CK(cudaEventCreateWithFlags(&ctx->ev_pyr, cudaEventDisableTiming));
+    }
+    if (const char* v = getenv("SVO_GPU_STEP_PYR_ASYNC")) ctx->pyr_async = atoi(v);
     if (const char* v = getenv("SVO_GPU_BUCKET_MODE")) ctx->bb.mode = atoi(v);   // 1: global-memory kernels, 2: one CTA per lane
     if (const char* v = getenv("SVO_GPU_STEP_OVERLAP")) ctx->overlap = atoi(v);
     if (const char* v = getenv("SVO_GPU_KLT_RESERVE")) ctx->klt_reserve = atoi(v);
@@ -340,6 +354,8 @@ extern "C" int svo_gpu_destroy(svo_gpu_ctx* ctx)
     if (ctx->ev_klt) cudaEventDestroy(ctx->ev_klt);
     if (ctx->ev_out) cudaEventDestroy(ctx->ev_out);
     if (ctx->aux_st) { cudaStreamSynchronize(ctx->aux_st); cudaStreamDestroy(ctx->aux_st); }
+    if (ctx->pyr_st) { cudaStreamSynchronize(ctx->pyr_st); cudaStreamDestroy(ctx->pyr_st); }
+    if (ctx->ev_pyr) cudaEventDestroy(ctx->ev_pyr);
     if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
     if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
     for (auto& tk : ctx->tickets) {
@@ -347,6 +363,7 @@ extern "C" int svo_gpu_destroy(svo_gpu_ctx* ctx)
         if (tk.done) cudaEventDestroy(tk.done);
         for (auto& e : tk.ev) if (e) cudaEventDestroy(e);
         for (auto& e : tk.eva) if (e) cudaEventDestroy(e);
+        if (tk.evk) cudaEventDestroy(tk.evk);
     }
     for (auto& e : ctx->ev_raw_free) if (e) cudaEventDestroy(e);
     for (auto& s : ctx->slots) {
@@ -507,8 +524,10 @@ extern "C" int svo_gpu_download_image(svo_gpu_ctx* ctx, int slot, int lane, uint
 }
 
 // enqueue only (no synchronisation): ingest + pyrDown chain of every lane of the slot
-static int enqueue_pyramid(svo_gpu_ctx* ctx, Slot& s, int win_w, int win_h, int max_level, int* levels_out)
+static int enqueue_pyramid(svo_gpu_ctx* ctx, Slot& s, int win_w, int win_h, int max_level, int* levels_out,
+                           cudaStream_t ps = nullptr)
 {
+    if (!ps) ps = ctx->st;
     if (!s.uploaded) return fail(ctx, SVO_GPU_E_STATE, "slot has no image");
     if (win_w <= 2 || win_h <= 2 || win_w > SVO_GPU_MAX_WIN || win_h > SVO_GPU_MAX_WIN)
         return fail(ctx, win_w <= 2 || win_h <= 2 ? SVO_GPU_E_ARG : SVO_GPU_E_UNSUPPORTED, "window %dx%d outside 3..%d",
@@ -519,8 +538,8 @@ static int enqueue_pyramid(svo_gpu_ctx* ctx, Slot& s, int win_w, int win_h, int 
     make_geometry(s.g, s.w, s.h, eff + 1, margin_for(win_w, win_h));
     if (int r = ensure(ctx, s.pyr, (size_t)s.g.lane_bytes * (size_t)ctx->max_batch)) return r;
     uint8_t* pyr = static_cast<uint8_t*>(s.pyr.p);
-    launch_ingest(ctx->st, s.raw, s.raw_pitch, s.raw_lane, pyr, s.g, s.batch, &ctx->launches);
-    for (int l = 1; l <= eff; ++l) launch_pyrdown(ctx->st, pyr, s.g, l, s.batch, &ctx->launches);
+    launch_ingest(ps, s.raw, s.raw_pitch, s.raw_lane, pyr, s.g, s.batch, &ctx->launches);
+    for (int l = 1; l <= eff; ++l) launch_pyrdown(ps, pyr, s.g, l, s.batch, &ctx->launches);
     CK(cudaGetLastError());
     s.pyr_built = true;
     s.win_w = win_w; s.win_h = win_h;
