@@ -68,6 +68,27 @@ def test_step_detection_beside_tracking(oracle, monkeypatch):
         assert all(m > 0 for m in ms) and ctx.last_klt_iterations > 0
 
 
+def test_step_pyramid_on_main_stream(oracle, monkeypatch):
+    """SVO_GPU_STEP_PYR_ASYNC=0: the pyramid is built on the main stream instead of the high-priority one (the default, which
+    every other test of this file exercises).  Same answers, with two steps outstanding."""
+    import torch
+    from oracle.cpu_pipeline import CpuFrontend
+    monkeypatch.setenv("SVO_GPU_STEP_PYR_ASYNC", "0")
+    seqs = _seqs(5)
+    B, T = seqs.shape[0], seqs.shape[1]
+    frames = torch.from_numpy(np.ascontiguousarray(seqs.transpose(1, 0, 2, 3))).pin_memory()
+    with capi.Context(max_w=W, max_h=H, max_levels=4, max_points=8192, max_batch=B) as ctx:
+        fe = Frontend(ctx, W, H, B, kp_capacity=8192, bucket_capacity=2048, max_tracks=400, mask_half=10.0)
+        cpus = [CpuFrontend(fe.pdict, impl="orc") for _ in range(B)]
+        fe.submit(frames[0].data_ptr(), None, capi.MEM_HOST, W, W * H)
+        for t in range(1, T + 1):
+            if t < T:
+                fe.submit(frames[t].data_ptr(), None, capi.MEM_HOST, W, W * H)
+            fe.wait()
+            for b in range(B):
+                _check_lane(fe, b, cpus[b].step(seqs[b, t - 1]), first=(t == 1))
+
+
 def test_step_device_memory_and_reset(oracle):
     import torch
     from oracle.cpu_pipeline import CpuFrontend
