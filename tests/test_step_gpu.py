@@ -194,6 +194,39 @@ def test_step_submit_wait_errors():
         assert int(fe.n_keypoints.sum()) > 0
 
 
+def test_two_contexts_interleaved(oracle):
+    """Two contexts on one device (two host threads' worth of state) driven alternately, with page-locked frames from
+    svo_gpu_host_alloc: neither disturbs the other (streams, events, work counters and buffers are per context)."""
+    import ctypes as C
+    from oracle.cpu_pipeline import CpuFrontend
+    seqs = _seqs(4)
+    B, T = seqs.shape[0], seqs.shape[1]
+    lib = capi.load()
+    p = C.c_void_p()
+    nbytes = B * W * H
+    assert lib.svo_gpu_host_alloc(C.byref(p), T * nbytes) == 0 and p.value
+    try:
+        host = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(T, B, H, W))
+        host[...] = seqs.transpose(1, 0, 2, 3)
+        with capi.Context(max_w=W, max_h=H, max_levels=4, max_points=8192, max_batch=B) as c1, \
+                capi.Context(max_w=W, max_h=H, max_levels=4, max_points=8192, max_batch=B) as c2:
+            f1 = Frontend(c1, W, H, B, kp_capacity=8192, bucket_capacity=2048, max_tracks=400, mask_half=10.0)
+            f2 = Frontend(c2, W, H, B, kp_capacity=8192, bucket_capacity=2048, max_tracks=300, mask_half=0.0)
+            cp1 = [CpuFrontend(f1.pdict, impl="orc") for _ in range(B)]
+            cp2 = [CpuFrontend(f2.pdict, impl="orc") for _ in range(B)]
+            for t in range(T):
+                f1.submit(p.value + t * nbytes, None, capi.MEM_HOST, W, W * H)
+                f2.submit(p.value + (T - 1 - t) * nbytes, None, capi.MEM_HOST, W, W * H)     # the sequences backwards
+                f2.wait()
+                f1.wait()
+                for b in range(B):
+                    _check_lane(f1, b, cp1[b].step(seqs[b, t]), first=(t == 0))
+                    _check_lane(f2, b, cp2[b].step(seqs[b, T - 1 - t]), first=(t == 0))
+    finally:
+        assert lib.svo_gpu_host_free(p) == 0
+    assert lib.svo_gpu_host_alloc(None, 16) != 0 and lib.svo_gpu_host_free(None) == 0
+
+
 def test_step_capacity_error():
     seqs = _seqs(1)
     with capi.Context(max_w=W, max_h=H, max_levels=4, max_points=8192, max_batch=3) as ctx:
