@@ -12,7 +12,7 @@ try:
     d = json.load(open(sys.argv[2]))
     print("%s streams %d: %.0f frames/s (e2e %.0f), %.3g tracks/s, step %.3f ms, stages %s, it/track %.1f, ok %.5f" % (
         sys.argv[1], d["config"]["streams_per_gpu"], d["value"], d["e2e"]["value"], d["klt_tracks_per_s"], d["ms_per_step"],
-        {k: round(v["ms"], 3) for k, v in d["kernels"].items()}, d["klt_issue_model"]["iterations_per_track"],
+        {k: round(v["ms"], 3) for k, v in d["kernels"].items() if isinstance(v, dict)}, d["klt_issue_model"]["iterations_per_track"],
         d["stats"]["status_ok_frac"]))
 except Exception as e:
     print(sys.argv[1], "FAILED", e)

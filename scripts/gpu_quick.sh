@@ -11,5 +11,5 @@ python - <<PY
 import json
 d = json.load(open("$OUT/bench.json"))
 print("value %.0f e2e %.0f ms/step %.4f" % (d["value"], d["e2e"]["value"], d["ms_per_step"]))
-print({k: round(v["ms"], 4) for k, v in d["kernels"].items()})
+print({k: round(v["ms"], 4) for k, v in d["kernels"].items() if isinstance(v, dict)})
 PY
