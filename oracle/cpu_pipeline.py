@@ -59,7 +59,7 @@ class CpuFrontend:
 
 
 def default_params(w, h, fast_threshold=20, bucket_size=32, per_bucket=5, max_tracks=2000, win=21, max_level=3,
-                   mask_half=0.0):
+                   mask_half=10.0):
     """The reference's settings: FAST 20 + NMS (include/config_reader.h:35-38), LK 21x21, maxLevel 3,
     {COUNT+EPS, 50, 0.001}, OPTFLOW_LK_GET_MIN_EIGENVALS (src/tracking.cpp:157-165)."""
     return dict(w=w, h=h, fast_threshold=fast_threshold, fast_nms=1, mask_half=mask_half, bucket_size=bucket_size,

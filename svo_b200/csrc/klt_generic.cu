@@ -13,8 +13,8 @@
 //   - status cleared only by level-0 outcomes; results are not clipped to the image.
 //
 // Design for sm_100a (the kernel is instruction-issue bound, not HBM bound: its footprint, two pyramids, lives in L2):
-//   - the I patch, Ix, Iy of the feature live in REGISTERS (ceil(w*h/32) pixels per lane) for the compiled window
-//     sizes (21x21, 11x11, 31x31); other sizes take the generic instantiation (patch in shared memory)
+//   - the I patch, Ix, Iy of the feature live in shared memory as int16 (the compiled windows of klt.cu keep them in
+//     registers)
 //   - source regions are staged per warp in shared memory with aligned 32-bit loads from the REFLECT_101-margined
 //     pyramid (no bounds logic), all loads of a region in flight before the first store
 //   - the reference's int16x2 Scharr derivative images are never materialised: because bilinear interpolation and the
@@ -31,15 +31,12 @@ namespace {
 
 using namespace lk;
 
-// Window geometry: compile-time for the specialised kernels (WW > 0), runtime otherwise.
-template <int WW, int WH>
+// Window geometry (runtime).
 struct Geo {
-    static constexpr bool kFixed = WW > 0;
-    static constexpr int kNPL = kFixed ? (WW * WH + 31) / 32 : 1;   // patch pixels per lane (register-resident)
     int ww_, wh_;
     __device__ __forceinline__ Geo(int w, int h) : ww_(w), wh_(h) {}
-    __device__ __forceinline__ int ww() const { return kFixed ? WW : ww_; }
-    __device__ __forceinline__ int wh() const { return kFixed ? WH : wh_; }
+    __device__ __forceinline__ int ww() const { return ww_; }
+    __device__ __forceinline__ int wh() const { return wh_; }
     __device__ __forceinline__ int npx() const { return ww() * wh(); }
     __device__ __forceinline__ int nwords() const { return (ww() + 9) >> 2; }      // words per staged row
     __device__ __forceinline__ int rpitch() const { return nwords() * 4; }          // bytes per staged row
@@ -49,9 +46,8 @@ struct Geo {
 };
 
 // Stages `nrows` rows of nwords aligned 32-bit words, starting at the word holding column x0 of row y0, into sm
-// (row-major, nwords per row).  Lane (r0, c0) = (lane / nwords, lane % nwords) walks rows r0, r0 + rpi, ...; all loads
-// are issued before the first store.  Returns the byte offset (0..3) of column x0 inside the first word.
-template <int MAXIT>
+// (row-major, nwords per row).  Lane (r0, c0) = (lane / nwords, lane % nwords) walks rows r0, r0 + rpi, ...
+// walk its rows in turn.  Returns the byte offset (0..3) of column x0 inside the first word.
 __device__ __forceinline__ int stage_region(uint32_t* __restrict__ sm, const uint8_t* __restrict__ origin, int pitch,
                                             int x0, int y0, int nrows, int nwords, int r0, int c0, int rpi)
 {
@@ -60,39 +56,19 @@ __device__ __forceinline__ int stage_region(uint32_t* __restrict__ sm, const uin
     const long long step = (long long)rpi * pitch;
     uint32_t* dst = sm + r0 * nwords + c0;
     const int dstep = rpi * nwords;
-    if constexpr (MAXIT > 0) {
-        uint32_t v[MAXIT];
-#pragma unroll
-        for (int k = 0; k < MAXIT; ++k)
-            if (r0 + k * rpi < nrows) v[k] = __ldg(reinterpret_cast<const uint32_t*>(src + k * step));
-#pragma unroll
-        for (int k = 0; k < MAXIT; ++k)
-            if (r0 + k * rpi < nrows) dst[k * dstep] = v[k];
-    } else {
-        for (int r = r0; r < nrows; r += rpi, src += step, dst += dstep) *dst = __ldg(reinterpret_cast<const uint32_t*>(src));
-    }
+    for (int r = r0; r < nrows; r += rpi, src += step, dst += dstep) *dst = __ldg(reinterpret_cast<const uint32_t*>(src));
     return a;
 }
 
-template <int WW, int WH, int WARPS>
+template <int WARPS>
 __global__ void __launch_bounds__(WARPS * 32) klt_kernel(const KltArgs a)
 {
-    using G = Geo<WW, WH>;
-    constexpr bool FIXED = G::kFixed;
-    constexpr int NPL = G::kNPL;
-    const G g(a.win_w, a.win_h);
+    const Geo g(a.win_w, a.win_h);
     const int ww = g.ww(), wh = g.wh(), npx = g.npx();
     const int nwords = g.nwords(), rpitch = g.rpitch(), BP = g.bp();
     const int region_words = g.region_words(), plane_words = g.plane_words();
-    // compile-time trip counts of the staging loops (0 = runtime loop)
-    constexpr int NW_CT = FIXED ? ((WW + 9) >> 2) : 1;
-    constexpr int RPI_CT = 32 / NW_CT;
-    constexpr int IT_I = FIXED ? (WH + 3 + RPI_CT - 1) / RPI_CT : 0;   // (wh+3)-row region of the previous image
-    constexpr int IT_J = FIXED ? (WH + 1 + RPI_CT - 1) / RPI_CT : 0;   // (wh+1)-row region of the next image
 
     extern __shared__ __align__(16) uint32_t smem_dyn[];
-    constexpr int kStaticWords = FIXED ? WARPS * ((WH + 3) * ((WW + 9) >> 2) + (WW + 2) * (WH + 2)) : 1;
-    __shared__ __align__(16) uint32_t smem_static[kStaticWords];
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int lane_id = blockIdx.y;
@@ -100,10 +76,10 @@ __global__ void __launch_bounds__(WARPS * 32) klt_kernel(const KltArgs a)
     const int pt = blockIdx.x * WARPS + warp;
     if (pt >= n) return;
 
-    const int per_warp_words = region_words + plane_words + (FIXED ? 0 : (3 * npx + 1) / 2);
-    uint32_t* region = (FIXED ? smem_static : smem_dyn) + warp * per_warp_words;
+    const int per_warp_words = region_words + plane_words + (3 * npx + 1) / 2;
+    uint32_t* region = smem_dyn + warp * per_warp_words;
     int* plane = reinterpret_cast<int*>(region + region_words);   // B plane (fast path) or packed Scharr plane (border path)
-    short* pIw = reinterpret_cast<short*>(plane + plane_words);   // generic kernel only
+    short* pIw = reinterpret_cast<short*>(plane + plane_words);
     short* pIx = pIw + npx;
     short* pIy = pIx + npx;
     const uint8_t* rbytes = reinterpret_cast<const uint8_t*>(region);
@@ -116,19 +92,6 @@ __global__ void __launch_bounds__(WARPS * 32) klt_kernel(const KltArgs a)
     // plane map of this lane: element lane + 32 i sits at (u, v), advanced incrementally (no divisions in the loops)
     const int pl_v0 = lane / BP, pl_u0 = lane - pl_v0 * BP;
     const int pl_du = 32 % BP, pl_dv = 32 / BP;
-
-    // register-resident patch of the compiled windows: pixel q = lane + 32 k
-    int offI[NPL];
-    int Iw[NPL], Ix[NPL], Iy[NPL];
-    if constexpr (FIXED) {
-#pragma unroll
-        for (int k = 0; k < NPL; ++k) {
-            int q = lane + 32 * k;
-            if (q >= WW * WH) q = 0;   // padding slot: reads pixel 0 and contributes nothing (Ix = Iy = 0)
-            const int y = q / WW;
-            offI[k] = y * rpitch + (q - y * WW);
-        }
-    }
 
     const size_t pbase = (size_t)lane_id * a.pts_lane + pt;
     const float2 prev = a.prev_xy[pbase];
@@ -161,7 +124,7 @@ __global__ void __launch_bounds__(WARPS * 32) klt_kernel(const KltArgs a)
 
         // ---- stage the (ww+3) x (wh+3) region of I whose top-left is (ipx-1, ipy-1)
         __syncwarp();
-        int ao = stage_region<IT_I>(region, Ppyr + L.off, L.pitch, ipx - 1, ipy - 1, wh + 3, nwords, st_r0, st_c0, rpi);
+        int ao = stage_region(region, Ppyr + L.off, L.pitch, ipx - 1, ipy - 1, wh + 3, nwords, st_r0, st_c0, rpi);
         __syncwarp();
         const uint8_t* rb = rbytes + ao;
 
@@ -189,23 +152,11 @@ __global__ void __launch_bounds__(WARPS * 32) klt_kernel(const KltArgs a)
                 ixv = descale(3 * ((ne_ - nw_) + (se_ - sw_)) + 10 * (e_ - w_), kWBits);
                 iyv = descale(3 * ((sw_ - nw_) + (se_ - ne_)) + 10 * (s_ - n_), kWBits);
             };
-            if constexpr (FIXED) {
-#pragma unroll
-                for (int k = 0; k < NPL; ++k) {
-                    const bool valid = lane + 32 * k < WW * WH;
-                    int iv, ixv, iyv;
-                    fast_px(valid ? lane + 32 * k : 0, iv, ixv, iyv);
-                    if (!valid) { ixv = 0; iyv = 0; }
-                    Iw[k] = iv; Ix[k] = ixv; Iy[k] = iyv;
-                    sA11 += ixv * ixv; sA12 += ixv * iyv; sA22 += iyv * iyv;
-                }
-            } else {
-                for (int q = lane; q < npx; q += 32) {
-                    int iv, ixv, iyv;
-                    fast_px(q, iv, ixv, iyv);
-                    pIw[q] = (short)iv; pIx[q] = (short)ixv; pIy[q] = (short)iyv;
-                    sA11 += ixv * ixv; sA12 += ixv * iyv; sA22 += iyv * iyv;
-                }
+            for (int q = lane; q < npx; q += 32) {
+                int iv, ixv, iyv;
+                fast_px(q, iv, ixv, iyv);
+                pIw[q] = (short)iv; pIx[q] = (short)ixv; pIy[q] = (short)iyv;
+                sA11 += ixv * ixv; sA12 += ixv * iyv; sA22 += iyv * iyv;
             }
         } else {
             // ---- border path: Scharr plane at (ipx..ipx+ww, ipy..ipy+wh), ZERO outside the image (calcScharrDeriv +
@@ -241,25 +192,11 @@ __global__ void __launch_bounds__(WARPS * 32) klt_kernel(const KltArgs a)
                                   (int)(short)(d10 & 0xffff) * w.w10 + (int)(short)(d11 & 0xffff) * w.w11, kWBits);
                 iyv = descale((d00 >> 16) * w.w00 + (d01 >> 16) * w.w01 + (d10 >> 16) * w.w10 + (d11 >> 16) * w.w11, kWBits);
             };
-            if constexpr (FIXED) {
-#pragma unroll 1
-                for (int k = 0; k < NPL; ++k) {   // rare path: keep it small (not unrolled); dynamic register indexing
-                    const bool valid = lane + 32 * k < WW * WH;   // is avoided by the switch-free select chain below
-                    int iv, ixv, iyv;
-                    slow_px(valid ? lane + 32 * k : 0, iv, ixv, iyv);
-                    if (!valid) { ixv = 0; iyv = 0; }
-#pragma unroll
-                    for (int j = 0; j < NPL; ++j)
-                        if (j == k) { Iw[j] = iv; Ix[j] = ixv; Iy[j] = iyv; }
-                    sA11 += ixv * ixv; sA12 += ixv * iyv; sA22 += iyv * iyv;
-                }
-            } else {
-                for (int q = lane; q < npx; q += 32) {
-                    int iv, ixv, iyv;
-                    slow_px(q, iv, ixv, iyv);
-                    pIw[q] = (short)iv; pIx[q] = (short)ixv; pIy[q] = (short)iyv;
-                    sA11 += ixv * ixv; sA12 += ixv * iyv; sA22 += iyv * iyv;
-                }
+            for (int q = lane; q < npx; q += 32) {
+                int iv, ixv, iyv;
+                slow_px(q, iv, ixv, iyv);
+                pIw[q] = (short)iv; pIx[q] = (short)ixv; pIy[q] = (short)iyv;
+                sA11 += ixv * ixv; sA12 += ixv * iyv; sA22 += iyv * iyv;
             }
         }
         const float A11 = __fmul_rn(__ll2float_rn(warp_sum_exact(sA11)), FLT_SCALE);
@@ -283,20 +220,11 @@ __global__ void __launch_bounds__(WARPS * 32) klt_kernel(const KltArgs a)
         // diff*Ix, diff*Iy (Newton step) or |diff| (L1 residual)
         auto window_pass = [&](const uint8_t* jb, int& s1, int& s2, bool l1) {
             s1 = 0; s2 = 0;
-            if constexpr (FIXED) {
-#pragma unroll
-                for (int k = 0; k < NPL; ++k) {
-                    const int diff = ((bilin(jb + offI[k], rpitch, w) + (1 << (kWBits - 6))) >> (kWBits - 5)) - Iw[k];
-                    if (l1) { if (lane + 32 * k < WW * WH) s1 += abs(diff); }
-                    else { s1 += diff * Ix[k]; s2 += diff * Iy[k]; }
-                }
-            } else {
-                for (int q = lane; q < npx; q += 32) {
-                    const int y = q / ww, x = q - y * ww;
-                    const int diff = descale(bilin(jb + y * rpitch + x, rpitch, w), kWBits - 5) - (int)pIw[q];
-                    if (l1) s1 += abs(diff);
-                    else { s1 += diff * (int)pIx[q]; s2 += diff * (int)pIy[q]; }
-                }
+            for (int q = lane; q < npx; q += 32) {
+                const int y = q / ww, x = q - y * ww;
+                const int diff = descale(bilin(jb + y * rpitch + x, rpitch, w), kWBits - 5) - (int)pIw[q];
+                if (l1) s1 += abs(diff);
+                else { s1 += diff * (int)pIx[q]; s2 += diff * (int)pIy[q]; }
             }
         };
 
@@ -312,7 +240,7 @@ __global__ void __launch_bounds__(WARPS * 32) klt_kernel(const KltArgs a)
             ++iters;
             w = bilinear_weights(__fsub_rn(nx, (float)inx), __fsub_rn(ny, (float)iny));
             __syncwarp();
-            ao = stage_region<IT_J>(region, Jorigin, L.pitch, inx, iny, wh + 1, nwords, st_r0, st_c0, rpi);
+            ao = stage_region(region, Jorigin, L.pitch, inx, iny, wh + 1, nwords, st_r0, st_c0, rpi);
             __syncwarp();
             int sb1, sb2;
             window_pass(rbytes + ao, sb1, sb2, false);
@@ -341,7 +269,7 @@ __global__ void __launch_bounds__(WARPS * 32) klt_kernel(const KltArgs a)
             }
             w = bilinear_weights(__fsub_rn(qx, (float)iqx), __fsub_rn(qy, (float)iqy));
             __syncwarp();
-            ao = stage_region<IT_J>(region, Jorigin, L.pitch, iqx, iqy, wh + 1, nwords, st_r0, st_c0, rpi);
+            ao = stage_region(region, Jorigin, L.pitch, iqx, iqy, wh + 1, nwords, st_r0, st_c0, rpi);
             __syncwarp();
             int serr, unused;
             window_pass(rbytes + ao, serr, unused, true);
@@ -366,9 +294,9 @@ void launch_klt_generic(cudaStream_t st, const KltArgs& a, int batch)
     const int ww = a.win_w, wh = a.win_h;
     const int words = (wh + 3) * ((ww + 9) >> 2) + (ww + 2) * (wh + 2) + (3 * ww * wh + 1) / 2;
     const size_t bytes = (size_t)WARPS * words * 4;
-    cudaFuncSetAttribute(klt_kernel<0, 0, WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+    cudaFuncSetAttribute(klt_kernel<WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
     dim3 grid((a.n_max + WARPS - 1) / WARPS, batch);
-    klt_kernel<0, 0, WARPS><<<grid, WARPS * 32, bytes, st>>>(a);
+    klt_kernel<WARPS><<<grid, WARPS * 32, bytes, st>>>(a);
 }
 
 }  // namespace svo

@@ -9,7 +9,7 @@ import numpy as np
 
 from . import capi
 
-REFERENCE_PARAMS = dict(fast_threshold=20, fast_nms=1, mask_half=0.0, bucket_size=32, per_bucket=5, max_tracks=2000,
+REFERENCE_PARAMS = dict(fast_threshold=20, fast_nms=1, mask_half=10.0, bucket_size=32, per_bucket=5, max_tracks=2000,
                         win_w=21, win_h=21, max_level=3, max_count=50, epsilon=0.001, criteria_type=3,
                         flags=capi.LK_GET_MIN_EIGENVALS, min_eig_threshold=1e-4)
 
