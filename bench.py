@@ -2,17 +2,24 @@
 """bench.py -- front-end frames/s of the svo per-frame feature front-end (FAST + bucketing + 4-level 21x21 KLT).
 
 One "step" = one frame of every stream on this GPU through svo_gpu_step (libsvo_gpu.so, C ABI): ingest + pyramid,
-LK from the previous frame on each stream's 2k tracks, FAST-9/16 + NMS on the new frame, grid bucketing, re-seeding of
-the tracks.  Workload = BASELINE.json's metric configuration (1241x376 KITTI-shaped synthetic frames, 2k tracks per
-stream) with `--streams` independent sequences per GPU (C5: 64).  Streams never interact, so N GPUs = N x streams
-sequences with no collective ("scaling": "weak"); torch.distributed is used for the start/stop barriers only.
+LK from the previous frame on each stream's 2k tracks, the +-10 px mask around those tracks, FAST-9/16 + NMS on the new
+frame, grid bucketing, re-seeding of the tracks (src/tracking.cpp:240-257 on a key-frame).  Workload = BASELINE.json's
+metric configuration (1241x376 KITTI-shaped synthetic frames, 2k tracks per stream) with `--streams` independent sequences
+per GPU (C5: 64).  Streams never interact, so N GPUs = N x streams sequences with no collective ("scaling": "weak");
+`--total-streams T` instead shards a FIXED set of T sequences over the ranks (BASELINE config 5 as written, "strong").
+torch.distributed is used for the start/stop barriers only.
 
   value : frames/s with the frames already resident in HBM (device ring larger than L2), CUDA events on the context's stream
   e2e   : frames/s through the same C-ABI call with HOST frames (pinned), H2D of every frame and D2H of the step's
           results (tracked points, status, err, bucketed features, counts) inside the timed region
-  --impl reference : the reference's own CPU path (OpenCV via cv2 + src/bucket.cpp compiled unmodified) on the host cores
+  single_stream : BASELINE config 1 (ONE sequence): ms/frame device-resident and end to end through the step API
+  drop_in       : config 1 through the reference-signature C++ wrappers (GpuFastDetector::detect ->
+                  FeatureSet::bucketingFeatures -> svo::calcOpticalFlowPyrLK on host cv::Mat frames)
+  --impl reference : the reference's own CPU path (OpenCV via cv2 + src/bucket.cpp compiled unmodified) on the host cores,
+                     one process per core (oracle/cpu_arm.py)
 """
 import argparse
+import hashlib
 import json
 import os
 import subprocess
@@ -29,6 +36,8 @@ sys.path.insert(0, ROOT)
 from svo_b200 import sharding, synth  # noqa: E402
 
 RING = 8   # frames per stream kept resident; time stamps 0,1,2,3,4,3,2,1 so that consecutive frames (and the wrap) are ~2 px apart
+METRIC = "front-end frames/s (FAST+bucketing+4-level 21x21 KLT, 2k tracks/stream)"
+DTYPE = "u8/int32 + f32 epilogue"
 
 
 def parse_args():
@@ -37,33 +46,49 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=300)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--streams", type=int, default=64, help="independent sequences per GPU")
+    ap.add_argument("--streams", type=int, default=64, help="independent sequences per GPU (weak scaling)")
+    ap.add_argument("--total-streams", type=int, default=0,
+                    help="strong scaling: a fixed set of this many sequences sharded over the ranks (config 5: 64)")
     ap.add_argument("--workload", default="C1", choices=sorted(synth.WORKLOADS), help="per-stream shape")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
+    ap.add_argument("--no-extras", action="store_true", help="skip the single_stream / drop_in / h2d_probe blocks")
+    ap.add_argument("--cpu-frames", type=int, default=12, help="frames per stream of the cpu_baseline aggregate sample")
+    ap.add_argument("--cpu-single-frames", type=int, default=50, help="frames of the single-sequence CPU figures (T = 1, T = all)")
     return ap.parse_args()
 
 
-def make_frames(wl, streams, seed0, rank=0):
-    """uint8 [RING, streams, h, w]: stream s = synthetic sequence with seed sharding.stream_seeds(rank, streams, seed0)[s]."""
-    seeds = sharding.stream_seeds(rank, streams, seed0)
+def stream_ids(args, rank, world):
+    """Global sequence ids this rank owns."""
+    if args.total_streams:
+        return sharding.sequences_of(rank, world, args.total_streams)
+    return list(range(rank * args.streams, (rank + 1) * args.streams))
+
+
+def make_frames(wl, ids, seed0):
+    """uint8 [RING, len(ids), h, w]: stream j = synthetic sequence with seed seed0 + ids[j]."""
     w, h = wl["w"], wl["h"]
     times = synth.ring_times(RING)
     distinct = sorted(set(times))
 
-    def one(s):
-        canvas = synth.make_canvas(w, h, seeds[s])
+    def one(g):
+        canvas = synth.make_canvas(w, h, seed0 + g)
         fr = {t: synth.render_frame(canvas, w, h, t) for t in distinct}
         return np.stack([fr[t] for t in times])
 
     with ThreadPoolExecutor(max_workers=min(16, os.cpu_count() or 1)) as ex:
-        seqs = list(ex.map(one, range(streams)))
+        seqs = list(ex.map(one, ids))
     return np.ascontiguousarray(np.stack(seqs, axis=1))
 
 
 def step_params(wl):
     return dict(fast_threshold=wl["fast_thr"], bucket_size=wl["bucket_size"], per_bucket=wl["per_bucket"],
-                max_tracks=wl["n_tracks"], win_w=wl["win"], win_h=wl["win"], max_level=wl["max_level"])
+                max_tracks=wl["n_tracks"], win_w=wl["win"], win_h=wl["win"], max_level=wl["max_level"], mask_half=10.0)
+
+
+def cpu_params(wl):
+    from oracle.cpu_pipeline import default_params
+    return default_params(wl["w"], wl["h"], wl["fast_thr"], wl["bucket_size"], wl["per_bucket"], wl["n_tracks"], wl["win"],
+                          wl["max_level"], mask_half=10.0)
 
 
 def pyramid_pixels(w, h, levels):
@@ -84,7 +109,7 @@ class ClockSampler:
         self.p = None
         try:
             self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
-                                       "--format=csv,noheader,nounits", "-lms", "50"], stdout=self.f,
+                                       "--format=csv,noheader,nounits", "-lms", "20"], stdout=self.f,
                                       stderr=subprocess.DEVNULL)
         except Exception:
             self.p = None
@@ -131,34 +156,41 @@ def dist_env():
     return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
 
 
+def workload_config(args, wl, world):
+    """Identical for both arms (the CPU arm's sample is described in its cpu_baseline block)."""
+    if args.total_streams:
+        what = "%d independent %dx%d synthetic sequences sharded over %d GPU(s)" % (args.total_streams, wl["w"], wl["h"], world)
+    else:
+        what = "%d independent %dx%d synthetic sequences per GPU" % (args.streams, wl["w"], wl["h"])
+    return {"workload": "C5-shaped: %s, %d tracks each (C1 per stream: mask +-10 px, FAST thr %d + NMS, bucketing %d px / %d "
+                        "per cell, KLT %dx%d, %d levels, 50 it / eps 0.001, min-eig err)" %
+                        (what, wl["n_tracks"], wl["fast_thr"], wl["bucket_size"], wl["per_bucket"], wl["win"], wl["win"],
+                         wl["max_level"] + 1),
+            "streams_per_gpu": args.streams if not args.total_streams else None,
+            "total_streams": args.total_streams or None,
+            "width": wl["w"], "height": wl["h"], "tracks_per_stream": wl["n_tracks"], "mask_half_px": 10,
+            "parallelism": "independent sequences per GPU, no collective",
+            "l2": "frame ring of %d frames per stream cycled (64 streams: 246 MB), larger than the 126 MB L2" % RING}
+
+
 # ------------------------------------------------------------------------------------------------ CPU arm
-def cpu_frontend_run(frames, wl, n_streams, n_steps, warmup, threads):
-    """The reference's CPU path (cv2 + compiled src/bucket.cpp, else the C port) on `n_streams` streams for
-    `warmup + n_steps` frames each, streams spread over `threads` host threads.  Returns (seconds of the timed steps,
-    frames processed in them, kind)."""
-    from oracle import oracle as O                     # bench.py's CPU arm is one of the places allowed to run oracle/
-    from oracle.cpu_pipeline import CpuFrontend, default_params
-    O.build()
-    impl = "cv2" if O.have_cv2() else "orc"
-    if impl == "cv2":
-        import cv2
-        cv2.setNumThreads(1 if n_streams >= threads else threads)   # parallelism across streams when there are enough
-    p = default_params(wl["w"], wl["h"], wl["fast_thr"], wl["bucket_size"], wl["per_bucket"], wl["n_tracks"], wl["win"],
-                       wl["max_level"])
-    fes = [CpuFrontend(p, impl) for _ in range(n_streams)]
-    pool = ThreadPoolExecutor(max_workers=max(1, min(threads, n_streams)))
-
-    def run_step(t):
-        list(pool.map(lambda s: fes[s].step(frames[t % RING, s]), range(n_streams)))
-
-    for t in range(warmup):
-        run_step(t)
-    t0 = time.perf_counter()
-    for t in range(warmup, warmup + n_steps):
-        run_step(t)
-    dt = time.perf_counter() - t0
-    pool.shutdown()
-    return dt, n_streams * n_steps, ("reference" if impl == "cv2" else "port")
+def cpu_baseline_block(wl, warmup, steps, single_frames=50):
+    """The reference's CPU path on this host (oracle/cpu_arm.py: processes, no per-keypoint Python) -> cpu_baseline dict."""
+    from oracle import cpu_arm                       # bench.py's CPU arm is one of the places allowed to run oracle/
+    rep = cpu_arm.full_report(wl, cpu_params(wl), wl["seed"] * 1000, warmup, steps, single_frames=single_frames)
+    agg, t1, tall = rep["aggregate"], rep["t1"], rep["tall"]
+    return {"value": agg["frames_per_s"], "unit": "frames/s", "cores": rep["cores"], "kind": agg["kind"],
+            "sample": "%d processes (one sequence each, cv2.setNumThreads(1)) x %d timed frames after %d warm-up frames, common "
+                      "start barrier; same per-stream workload as the GPU arm (mask on)" % (agg["processes"], steps, warmup),
+            "seconds": agg["seconds"], "python_overhead_frac": agg["python_overhead_frac"],
+            "stage_ms_median": agg["stage_ms_median"],
+            "single_sequence_1_thread": {"frames_per_s": t1["frames_per_s"], "ms_per_frame_median": t1["frame_ms_median"],
+                                         "stage_ms_median": t1["stage_ms_median"], "frames": t1["frames"]},
+            "single_sequence_all_threads": {"frames_per_s": tall["frames_per_s"], "ms_per_frame_median": tall["frame_ms_median"],
+                                            "stage_ms_median": tall["stage_ms_median"], "frames": tall["frames"],
+                                            "cv_threads": tall["cv_threads"],
+                                            "note": "the reference's own configuration: one stream, OpenCV parallel_for_ inside LK"},
+            "cv2": rep["cv2"]}
 
 
 def run_reference(args):
@@ -166,42 +198,118 @@ def run_reference(args):
     if rank != 0:
         return
     wl = synth.WORKLOADS[args.workload]
-    threads = os.cpu_count() or 1
-    # bounded sample of the same workload: as many streams as host threads (each stream is sequential in time)
-    n_streams = min(args.streams * args.gpus, max(threads, 1))
-    frames = make_frames(wl, n_streams, wl["seed"] * 1000)
-    dt, nframes, kind = cpu_frontend_run(frames, wl, n_streams, args.steps, args.warmup, threads)
-    fps = nframes / dt
+    cb = cpu_baseline_block(wl, args.warmup, args.steps, args.cpu_single_frames)
+    fps = cb["value"]
     line = {
-        "impl": "reference", "metric": "front-end frames/s (FAST+bucketing+4-level 21x21 KLT, 2k tracks/stream)",
-        "value": fps, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "u8/int32 + f32 epilogue", "data": "synthetic",
-        "config": workload_config(args, wl, note="CPU arm: %d streams per step on %d host threads" % (n_streams, threads)),
-        "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": threads, "kind": kind,
-                         "sample": "%d streams x %d frames, cv2.setNumThreads(1), %d stream threads" %
-                                   (n_streams, args.steps, min(threads, n_streams))},
+        "impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * cb["seconds"] / args.steps, "higher_is_better": True,
+        "scaling": "strong" if args.total_streams else "weak", "vs_baseline": None, "dtype": DTYPE, "data": "synthetic",
+        "config": workload_config(args, wl, max(world, args.gpus)),
+        "cpu_baseline": cb,
         "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
+        "notes": "CPU arm: a step = one frame of each of %d streams (one per host core); value = all frames / wall time "
+                 "between the common start and the last process's finish" % cb["cores"],
     }
     print(json.dumps(line))
 
 
-def workload_config(args, wl, note=None):
-    c = {"workload": "C5-shaped: %d independent %dx%d synthetic sequences per GPU, %d tracks each (C1 per stream: FAST thr %d "
-                     "+ NMS, bucketing %d px / %d per cell, KLT %dx%d, %d levels, 50 it / eps 0.001, min-eig err)" %
-                     (args.streams, wl["w"], wl["h"], wl["n_tracks"], wl["fast_thr"], wl["bucket_size"], wl["per_bucket"],
-                      wl["win"], wl["win"], wl["max_level"] + 1),
-         "streams_per_gpu": args.streams, "width": wl["w"], "height": wl["h"], "tracks_per_stream": wl["n_tracks"],
-         "parallelism": "independent sequences per GPU, no collective",
-         "l2": "frame ring of %d x %d frames (%.0f MB) cycled, larger than the 126 MB L2" %
-               (RING, args.streams, RING * args.streams * wl["h"] * 1280 / 1e6)}
-    if note:
-        c["note"] = note
-    return c
-
-
 # ------------------------------------------------------------------------------------------------ B200 arm
+def bind_near_gpu(local):
+    """Keeps this rank's host threads (and therefore its first-touch pinned pages) on the NUMA node of its GPU, when the box
+    has more than one; returns a description for the bench line.  No-op on single-node hosts."""
+    try:
+        bus = subprocess.run(["nvidia-smi", "-i", os.environ.get("CUDA_VISIBLE_DEVICES", "").split(",")[local] if
+                              os.environ.get("CUDA_VISIBLE_DEVICES") else str(local), "--query-gpu=pci.bus_id",
+                              "--format=csv,noheader"], capture_output=True, text=True, timeout=20).stdout.strip().lower()
+        if len(bus.split(":")[0]) == 8:       # 00000000:1b:00.0 -> 0000:1b:00.0 (sysfs form)
+            bus = bus[4:]
+        node = int(open("/sys/bus/pci/devices/%s/numa_node" % bus).read())
+        nodes = [d for d in os.listdir("/sys/devices/system/node") if d.startswith("node") and d[4:].isdigit()]
+        if node < 0 or len(nodes) < 2:
+            return {"numa_node": node, "numa_nodes": len(nodes), "bound": False}
+        cpus = set()
+        for part in open("/sys/devices/system/node/node%d/cpulist" % node).read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+        return {"numa_node": node, "numa_nodes": len(nodes), "bound": bool(cpus), "cpus": len(cpus)}
+    except Exception as e:
+        return {"bound": False, "error": repr(e)[:80]}
+
+
+def source_sha():
+    h = hashlib.sha1()
+    for f in ("klt.cu", "klt_common.cuh"):
+        h.update(open(os.path.join(ROOT, "svo_b200", "csrc", f), "rb").read())
+    return h.hexdigest()[:16]
+
+
+def run_single_stream(capi, Frontend, torch, local, wl, frames1, steps):
+    """BASELINE config 1: ONE sequence through the step API (1 lane), two steps outstanding.  -> dict."""
+    w, h = wl["w"], wl["h"]
+    pitch = (w + 127) // 128 * 128
+    n = max(steps, 50)
+    dev = torch.zeros((RING, 1, h, pitch), dtype=torch.uint8, device="cuda")
+    dev[..., :w] = torch.from_numpy(frames1).cuda()
+    host = torch.from_numpy(frames1).pin_memory()
+    cells = (h // wl["bucket_size"] + 1) * (w // wl["bucket_size"] + 1) * wl["per_bucket"]
+    out = {}
+    with capi.Context(device=local, max_w=w, max_h=h, max_levels=wl["max_level"] + 1, max_points=32768, max_batch=1) as ctx:
+        fe = Frontend(ctx, w, h, 1, bucket_capacity=cells, **step_params(wl))
+        stream = torch.cuda.ExternalStream(ctx.stream)
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+
+        def loop(i0, i1, submit, depth):
+            for i in range(i0, i1):
+                submit(i)
+                if fe.outstanding == depth:
+                    fe.wait()
+            while fe.outstanding:
+                fe.wait()
+
+        def sub_dev(i):
+            fe.submit(dev[i % RING].data_ptr(), None, capi.MEM_DEVICE, pitch, h * pitch, with_outputs=False)
+
+        def sub_host(i):
+            fe.submit(host[i % RING].data_ptr(), host[(i + 1) % RING].data_ptr(), capi.MEM_HOST, w, w * h)
+
+        for name, sub, depth in (("device_resident", sub_dev, 2), ("e2e", sub_host, 2), ("e2e_synchronous", sub_host, 1)):
+            fe.reset()
+            loop(0, 10, sub, depth)
+            torch.cuda.synchronize()
+            l0 = ctx.launch_count
+            t0 = time.perf_counter()
+            ev[0].record(stream)
+            loop(10, 10 + n, sub, depth)
+            ev[1].record(stream)
+            torch.cuda.synchronize()
+            wall = time.perf_counter() - t0
+            out[name] = {"ms_per_frame": ev[0].elapsed_time(ev[1]) / n, "wall_ms_per_frame": 1e3 * wall / n,
+                         "frames_per_s": n / wall, "launches_per_frame": (ctx.launch_count - l0) / n}
+        out["frames"] = n
+        out["note"] = ("one 1241x376 sequence, 2k tracks, through svo_gpu_step_submit/_wait; e2e_synchronous = each frame's "
+                       "results are on the host before the next frame is submitted (the reference's loop, src/tracking.cpp:240-268)")
+    return out
+
+
+def run_drop_in(wl):
+    """Config 1 through the C++ wrappers with the reference's signatures (svo_b200/host/frontend_selftest --bench)."""
+    exe = os.path.join(ROOT, "svo_b200", "lib", "frontend_selftest")
+    if not os.path.exists(exe):
+        return {"unavailable": "svo_b200/lib/frontend_selftest not built"}
+    try:
+        r = subprocess.run([exe, "--bench", "200"], capture_output=True, text=True, timeout=300)
+        for line in r.stdout.splitlines():
+            if line.startswith("{"):
+                return json.loads(line)
+        return {"unavailable": "no JSON line (rc %d): %s" % (r.returncode, (r.stdout + r.stderr)[-200:])}
+    except Exception as e:
+        return {"unavailable": repr(e)[:200]}
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -212,6 +320,7 @@ def run_b200(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the front-end has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
+    binding = bind_near_gpu(local)
     if world > 1:
         # stdout carries exactly one JSON line: NCCL's version banner (NCCL_DEBUG=VERSION on some boxes) goes to stderr
         if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", "WARN"):
@@ -219,11 +328,13 @@ def run_b200(args):
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     wl = synth.WORKLOADS[args.workload]
-    w, h, S, K, W = wl["w"], wl["h"], args.streams, args.steps, args.warmup
+    ids = stream_ids(args, rank, world)
+    w, h, S, K, W = wl["w"], wl["h"], len(ids), args.steps, args.warmup
+    total_streams = args.total_streams or world * args.streams
     levels = wl["max_level"] + 1
     pitch = (w + 127) // 128 * 128
 
-    frames = make_frames(wl, S, wl["seed"] * 1000, rank)                  # [RING, S, h, w]
+    frames = make_frames(wl, ids, wl["seed"] * 1000)                     # [RING, S, h, w]
     dev = torch.zeros((RING, S, h, pitch), dtype=torch.uint8, device="cuda")
     dev[..., :w] = torch.from_numpy(frames).cuda()
     host = torch.from_numpy(frames).pin_memory()                         # compact rows, like a cv::Mat
@@ -234,7 +345,7 @@ def run_b200(args):
                        max_batch=S)
     fe = Frontend(ctx, w, h, S, bucket_capacity=cells, **step_params(wl))
     stream = torch.cuda.ExternalStream(ctx.stream)
-    ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(6)]
 
     def barrier():
         torch.cuda.synchronize()
@@ -247,10 +358,10 @@ def run_b200(args):
     # Both timed loops drive the step through svo_gpu_step_submit / svo_gpu_step_wait with two steps outstanding: step i+1 is
     # enqueued before the host waits for step i (frame i+1 never needs frame i's results on the HOST: the tracks are re-seeded
     # on the device), so the device does not idle while the host handles a frame.  Every step's results are waited for.
-    def run_steps(i0, i1, submit, after_wait=None):
+    def run_steps(i0, i1, submit, after_wait=None, depth=2):
         for i in range(i0, i1):
             submit(i)
-            if fe.outstanding == 2:
+            if fe.outstanding == depth:
                 fe.wait()
                 if after_wait:
                     after_wait()
@@ -283,6 +394,26 @@ def run_b200(args):
         kp_sum += int(fe.n_keypoints.sum()); bk_sum += int(fe.n_bucketed.sum()); trk_sum += int(fe.n_tracked.sum())
         ok_sum += int(sum(int(fe.status[b, :fe.n_tracked[b]].sum()) for b in range(S)))
 
+    # ---- H2D alone (same frames, same pinned ring, no kernels): names the limiter of e2e when ranks share a host
+    h2d = None
+    if not args.no_extras:
+        scratch = torch.empty((S, h, w), dtype=torch.uint8, device="cuda")
+        cs = torch.cuda.Stream()
+        with torch.cuda.stream(cs):
+            for i in range(3):
+                scratch.copy_(host[i % RING], non_blocking=True)
+            barrier()
+            ev[4].record(cs)
+            for i in range(40):
+                scratch.copy_(host[i % RING], non_blocking=True)
+            ev[5].record(cs)
+        barrier()
+        h2d_ms = max_over_ranks(ev[4].elapsed_time(ev[5])) / 40
+        h2d = {"ms_per_step": h2d_ms, "gb_per_s_per_gpu": S * w * h / (h2d_ms * 1e-3) / 1e9,
+               "gb_per_s_all_gpus": world * S * w * h / (h2d_ms * 1e-3) / 1e9,
+               "note": "one step's frames (pinned host ring) copied alone, no kernels, all ranks at once, max over ranks"}
+        del scratch
+
     # ---- device resident: frames already in HBM, nothing returned to the host
     sampler = ClockSampler(local) if rank == 0 else None   # nvidia-smi needs a moment to start: launched before the warm-up
     def submit_dev(i):
@@ -290,32 +421,38 @@ def run_b200(args):
 
     fe.reset()
     run_steps(0, W, submit_dev)
-    ctx.step_profile(True)
     launches0 = ctx.launch_count
     barrier()
     t_start = time.time()
     ev[2].record(stream)
-    acc = {"stage": np.zeros(4), "iters": 0}
+    acc = {"stage": np.zeros(4), "iters": 0, "n": 0}
 
     def after_wait():
         acc["stage"] += np.array(ctx.step_profile(True))
         acc["iters"] += ctx.last_klt_iterations
+        acc["n"] += 1
 
-    run_steps(W, W + K, submit_dev, after_wait)
-    stage, iters = acc["stage"], acc["iters"]
+    run_steps(W, W + K, submit_dev)
     ev[3].record(stream)
     barrier()
-    clocks = sampler.stop(t_start, time.time()) if sampler else None
+    t_stop = time.time()
     dev_ms = max_over_ranks(ev[2].elapsed_time(ev[3]))
     launches = ctx.launch_count - launches0
+    # per-stage times: the same steps one at a time (one step outstanding), so that no stage of step t+1 runs beside a stage
+    # of step t and every CUDA-event bracket holds one stage alone.  Outside the timed region.
+    ctx.step_profile(True)
+    NP_ = 24
+    run_steps(W + K, W + K + NP_, submit_dev, after_wait, depth=1)
     ctx.step_profile(False)
+    clocks = sampler.stop(t_start, t_stop) if sampler else None
+    stage, iters = acc["stage"], acc["iters"]
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
 
-    frames_total = world * S * K
-    stage_ms = stage / K                                      # ingest+pyramid, LK, FAST, bucketing (per step, this rank)
+    frames_total = total_streams * K
+    stage_ms = stage / max(acc["n"], 1)                       # ingest+pyramid, LK, FAST (+mask), bucketing (per step, this rank)
     kp = kp_sum / (S * NS)
     n_trk = trk_sum / (S * NS)
     bk = bk_sum / (S * NS)
@@ -324,80 +461,92 @@ def run_b200(args):
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except Exception:
         pass
-    hbm_peak, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
+    hbm_peak, peak_src = (peaks["hbm_gbs"], "MEASURED_PEAKS.json") if "hbm_gbs" in peaks else (6650.0, "fallback of B200_PROFILING.md")
     npyr = pyramid_pixels(w, h, levels)
     # algorithmic bytes per launch group (SURVEY.md section 8d x the streams one launch covers)
     alg = {
         "pyramid": S * npyr,                                  # read level 0 once + write levels >= 1
         "klt": S * (2 * npyr + 29 * n_trk),                   # both pyramids once + per-track in/out
-        "fast": S * (w * h + 12 * kp),
+        "fast": S * (2 * w * h + 12 * kp),                    # image + full mask read (m = 1) + 12 B per keypoint
         "bucket": S * 12 * (kp + bk),
     }
     names = ["pyramid", "klt", "fast", "bucket"]
     kernels = {n: {"ms": float(stage_ms[i]), "alg_bytes": float(alg[n]),
                    "achieved_gbs": float(alg[n] / (stage_ms[i] * 1e-3) / 1e9) if stage_ms[i] > 0 else None}
                for i, n in enumerate(names)}
-    traffic = ncu = None
+    ncu = {}
     try:
         ncu = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
-        traffic = ncu.get("klt_kernel")
     except Exception:
         pass
+    ncu_fresh = ncu.get("klt_source_sha") == source_sha()     # the capture is of THIS klt.cu
     klt = kernels["klt"]
-    it_per_track = iters / max(S * n_trk * K, 1)
+    it_per_track = iters / max(S * n_trk * acc["n"], 1)
     # op model of SURVEY 8d: 18 lane-ops per setup pixel per level, 8 per iteration pixel
     lane_ops = (levels * wl["win"] ** 2 * 18 + it_per_track * wl["win"] ** 2 * 8) * n_trk * S
     sm_mhz = (clocks or {}).get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)
+    lane_peak = 148 * 128 * sm_mhz * 1e6
+    ach_ops = lane_ops / (klt["ms"] * 1e-3) if klt["ms"] > 0 else None
+    kname = "klt_run_kernel<%d,%d,...>" % (wl["win"], wl["win"])
+    roof = {"kernel": kname, "bound": "sm_issue", "achieved": ach_ops, "peak": lane_peak, "unit": "lane-op/s",
+            "frac": (ach_ops or 0) / lane_peak,
+            "traffic": ncu.get("klt_kernel") if ncu_fresh else None,
+            "model": "SURVEY 8d: 18 lane-ops per set-up pixel per level + 8 per iteration pixel, measured iterations per track; "
+                     "peak = 148 SMs x 128 lanes x the SM clock sampled during the timed region",
+            "iterations_per_track": it_per_track, "lane_ops_per_launch": lane_ops, "launch_ms": klt["ms"],
+            "hbm": {"achieved": klt["achieved_gbs"], "peak": hbm_peak, "unit": "GB/s", "frac": (klt["achieved_gbs"] or 0) / hbm_peak,
+                    "peak_source": peak_src, "alg_bytes_per_launch": klt["alg_bytes"],
+                    "note": "for the contract: LK's footprint (two pyramids) lives in L2; HBM is not its bound"}}
+    if ncu_fresh and ncu.get("klt_warp_inst_per_launch") and S == 64 and wl["n_tracks"] == 2000 and klt["ms"] > 0:
+        peak_issue = 148 * 4 * sm_mhz * 1e6
+        ach = ncu["klt_warp_inst_per_launch"] / (klt["ms"] * 1e-3)
+        roof["issue_slots"] = {"achieved": ach, "peak": peak_issue, "unit": "warp-inst/s", "frac": ach / peak_issue,
+                               "warp_inst_per_launch": ncu["klt_warp_inst_per_launch"],
+                               "warp_inst_per_track": ncu["klt_warp_inst_per_launch"] / (S * n_trk),
+                               "source": "instructions: ncu smsp__inst_executed.sum of this klt.cu (profiles/ncu_traffic.json, "
+                                         "source hash checked); time: live CUDA events"}
     line = {
-        "metric": "front-end frames/s (FAST+bucketing+4-level 21x21 KLT, 2k tracks/stream)",
+        "metric": METRIC,
         "value": frames_total / (dev_ms * 1e-3), "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": W,
-        "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "u8/int32 + f32 epilogue", "data": "synthetic", "config": workload_config(args, wl),
+        "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "strong" if args.total_streams else "weak",
+        "vs_baseline": None, "dtype": DTYPE, "data": "synthetic", "config": workload_config(args, wl, world),
         "e2e": {"value": frames_total / (e2e_ms * 1e-3), "unit": "frames/s", "h2d_bytes_per_step": S * w * h,
                 "d2h_bytes_per_step": fe.d2h_bytes, "ms_per_step": e2e_ms / K},
         "gpu_launches": int(launches),
         "clocks": clocks,
-        "roofline": {"kernel": "klt_kernel<21,21,8>", "bound": "hbm", "achieved": klt["achieved_gbs"], "peak": hbm_peak,
-                     "unit": "GB/s", "frac": (klt["achieved_gbs"] or 0) / hbm_peak, "traffic": traffic,
-                     "peak_source": peak_src,
-                     "note": "LK is not HBM-bound: its footprint (two pyramids) lives in L2; its bound is the SM issue "
-                             "rate, see roofline.issue and klt_issue_model"},
-        "klt_issue_model": {"iterations_per_track": it_per_track, "lane_ops_per_launch": lane_ops,
-                            "achieved_lane_ops_per_s": lane_ops / (klt["ms"] * 1e-3) if klt["ms"] > 0 else None,
-                            "peak_lane_ops_per_s": 148 * 128 * sm_mhz * 1e6,
-                            "frac": (lane_ops / (klt["ms"] * 1e-3)) / (148 * 128 * sm_mhz * 1e6) if klt["ms"] > 0 else None},
+        "roofline": roof,
+        "rooflines": {n: {"bound": "hbm", "achieved": kernels[n]["achieved_gbs"], "peak": hbm_peak, "unit": "GB/s",
+                          "frac": (kernels[n]["achieved_gbs"] or 0) / hbm_peak, "ms": kernels[n]["ms"],
+                          "alg_bytes_per_launch": kernels[n]["alg_bytes"]} for n in ("pyramid", "fast", "bucket")},
         "kernels": kernels,
         "stats": {"keypoints_per_frame": kp, "bucketed_per_frame": bk, "tracks_per_frame": n_trk,
-                  "status_ok_frac": ok_sum / max(trk_sum, 1)},
+                  "status_ok_frac": ok_sum / max(trk_sum, 1), "streams_this_rank": S},
     }
-    line["klt_tracks_per_s"] = world * S * n_trk * K / (dev_ms * 1e-3)
+    line["klt_tracks_per_s"] = total_streams * n_trk * K / (dev_ms * 1e-3)
     # stage-only rates (KLT-only and FAST-only reported next to the whole front-end), this rank's launches
     line["stage_rates"] = {
         "klt_only_tracks_per_s": S * n_trk / (klt["ms"] * 1e-3) if klt["ms"] > 0 else None,
         "fast_only_frames_per_s": S / (kernels["fast"]["ms"] * 1e-3) if kernels["fast"]["ms"] > 0 else None,
         "pyramid_only_frames_per_s": S / (kernels["pyramid"]["ms"] * 1e-3) if kernels["pyramid"]["ms"] > 0 else None,
         "bucket_only_frames_per_s": S / (kernels["bucket"]["ms"] * 1e-3) if kernels["bucket"]["ms"] > 0 else None,
-        "note": "per GPU; stage time = CUDA events around the stage's launches inside the timed region",
+        "note": "per GPU; stage time = CUDA events around the stage's launches",
     }
-    line["kernels"]["note"] = ("stage times are live CUDA-event brackets inside the timed region; the pyramid of step t+1 is "
-                               "built on a second stream beside FAST and bucketing of step t (SVO_GPU_STEP_PYR_ASYNC=1), so the "
-                               "pyramid and FAST brackets overlap each other and their sum exceeds ms_per_step; LK runs alone")
-    line["config"]["pipelining"] = "svo_gpu_step_submit / _wait, 2 steps outstanding; every step's results are waited for"
-    # the bound LK actually runs against: warp instructions issued per second.  Instructions per launch come from the ncu
-    # capture of this same workload (profiles/ncu_traffic.json, 64 x 2000 tracks), the launch time is measured here.
-    if ncu and ncu.get("klt_warp_inst_per_launch") and S == 64 and wl["n_tracks"] == 2000 and klt["ms"] > 0:
-        peak_issue = 148 * 4 * sm_mhz * 1e6
-        ach = ncu["klt_warp_inst_per_launch"] / (klt["ms"] * 1e-3)
-        line["roofline"]["issue"] = {"bound": "sm issue slots", "achieved": ach, "peak": peak_issue, "unit": "warp-inst/s",
-                                     "frac": ach / peak_issue, "warp_inst_per_launch": ncu["klt_warp_inst_per_launch"],
-                                     "source": "instructions: ncu smsp__inst_executed.sum (profiles/); time: live CUDA events"}
+    line["kernels"]["note"] = ("stage times are CUDA-event brackets over %d steps run one at a time right after the timed region "
+                               "(one step outstanding: every bracket holds one stage alone; in the timed region the pyramid of "
+                               "step t+1 runs beside FAST of step t); the FAST bracket includes the mask kernel" % NP_)
+    line["notes"] = {"pipelining": "svo_gpu_step_submit / _wait, 2 steps outstanding; every step's results are waited for",
+                     "host_binding": binding}
+    if h2d:
+        line["h2d_probe"] = h2d
+    if not args.no_extras:
+        try:
+            line["single_stream"] = run_single_stream(capi, Frontend, torch, local, wl, np.ascontiguousarray(frames[:, :1]), 200)
+        except Exception as e:   # an extra must never cost the headline line
+            line["single_stream"] = {"error": repr(e)[:200]}
+        if world == 1:
+            line["drop_in"] = run_drop_in(wl)
     if world == 1 and not args.no_cpu_baseline:
-        threads = os.cpu_count() or 1
-        ns = min(S, threads)
-        nsteps = max(4, int(args.cpu_seconds / 0.06 / ns))
-        dt, nfr, kind = cpu_frontend_run(frames, wl, ns, nsteps, 2, threads)
-        line["cpu_baseline"] = {"value": nfr / dt, "unit": "frames/s", "cores": threads, "kind": kind,
-                                "sample": "%d streams x %d frames of the same workload, one stream per host thread" % (ns, nsteps)}
+        line["cpu_baseline"] = cpu_baseline_block(wl, 3, args.cpu_frames, args.cpu_single_frames)
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

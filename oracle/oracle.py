@@ -209,13 +209,15 @@ def have_cv2():
         return False
 
 
-def cv2_fast(img, threshold=20, nms=True, mask=None):
-    """cv::FastFeatureDetector::create(threshold, nms)->detect(img, kps, mask)   (src/tracking.cpp:54-57, :82)."""
+def cv2_fast(img, threshold=20, nms=True, mask=None, with_response=True):
+    """cv::FastFeatureDetector::create(threshold, nms)->detect(img, kps, mask) + cv::KeyPoint::convert
+    (src/tracking.cpp:54-57, :82, :86).  The responses are read keypoint by keypoint in Python: parity tests only (the
+    timed CPU arm, oracle/cpu_arm.py, never asks for them)."""
     import cv2
     det = cv2.FastFeatureDetector_create(int(threshold), bool(nms))
     kps = det.detect(_img(img), _img(mask) if mask is not None else None)
-    xy = np.array([k.pt for k in kps], np.float32).reshape(-1, 2)
-    resp = np.array([k.response for k in kps], np.float32)
+    xy = cv2.KeyPoint_convert(kps).reshape(-1, 2).astype(np.float32) if len(kps) else np.zeros((0, 2), np.float32)
+    resp = np.array([k.response for k in kps], np.float32) if with_response else None
     return xy, resp
 
 
@@ -223,10 +225,11 @@ def cv2_build_mask(w, h, xy, half=10.0):
     """src/tracking.cpp:76-79."""
     import cv2
     mask = np.full((h, w), 255, np.uint8)
-    for x, y in np.asarray(xy, np.float32).reshape(-1, 2):
-        p1 = (int(np.rint(np.float32(x) - np.float32(half))), int(np.rint(np.float32(y) - np.float32(half))))
-        p2 = (int(np.rint(np.float32(x) + np.float32(half))), int(np.rint(np.float32(y) + np.float32(half))))
-        cv2.rectangle(mask, p1, p2, 0, cv2.FILLED)
+    xy = np.asarray(xy, np.float32).reshape(-1, 2)
+    p1 = np.rint(xy - np.float32(half)).astype(np.int64).tolist()   # float32 subtraction, then round-half-even (Point2f -> Point)
+    p2 = np.rint(xy + np.float32(half)).astype(np.int64).tolist()
+    for a, b in zip(p1, p2):
+        cv2.rectangle(mask, tuple(a), tuple(b), 0, cv2.FILLED)
     return mask
 
 

@@ -12,7 +12,7 @@ if [ "${2:-}" != "skip_tests" ]; then
 fi
 timeout 900 python bench.py > $OUT/bench.json 2> $OUT/bench.err; echo "bench rc=$?"
 cat $OUT/bench.json
-SHORT="python bench.py --steps 2 --warmup 3 --no-cpu-baseline"
+SHORT="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-extras"
 timeout 600 $SHORT > $OUT/plain.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $OUT/launches.csv $SHORT > $OUT/ncu_launch.log 2>&1
 echo "ncu launches rc=$?"

@@ -6,7 +6,7 @@ OUT=gpurun_out/$TAG
 mkdir -p $OUT
 timeout 900 python -m pytest tests -m gpu -x -q ${2:+-k "$2"} > $OUT/pytest.log 2>&1; echo "pytest rc=$?"
 tail -15 $OUT/pytest.log
-timeout 600 python bench.py --steps 100 --warmup 5 --no-cpu-baseline > $OUT/bench.json 2> $OUT/bench.err; echo "bench rc=$?"
+timeout 600 python bench.py --steps 100 --warmup 5 --no-cpu-baseline --no-extras > $OUT/bench.json 2> $OUT/bench.err; echo "bench rc=$?"
 python - <<PY
 import json
 d = json.load(open("$OUT/bench.json"))

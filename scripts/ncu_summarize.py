@@ -71,7 +71,12 @@ def kernels():
             tr["klt_warp_inst_per_launch"] = float(r[idx["smsp__inst_executed.sum"]])
             tr["klt_issue_active_pct_ncu"] = float(r[idx["smsp__issue_active.avg.pct_of_peak_sustained_active"]])
             tr["klt_workload_note"] = "64 streams x 2000 tracks (bench.py default workload)"
-    import json
+    import hashlib, json
+    h = hashlib.sha1()   # bench.py only trusts instruction counts captured from THIS klt.cu (same hash as bench.source_sha)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    for fn in ("klt.cu", "klt_common.cuh"):
+        h.update(open(os.path.join(root, "svo_b200", "csrc", fn), "rb").read())
+    tr["klt_source_sha"] = h.hexdigest()[:16]
     json.dump(tr, open(os.path.join(os.path.dirname(dst), "ncu_traffic.json"), "w"), indent=1)
     with open(dst + "_kernels.txt", "w") as f:
         f.write("# ncu --set full --clock-control none; source: %s/prof.ncu-rep (one row block per captured launch)\n" % src)

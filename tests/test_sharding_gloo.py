@@ -57,7 +57,7 @@ def test_reference_arm_prints_on_rank0_only():
     """bench.py --impl reference under a 2-rank launch: rank 0 runs and prints the CPU line, rank 1 exits 0 silently."""
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
            "--master-port", str(29600 + os.getpid() % 300), os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2",
-           "--steps", "1", "--warmup", "1", "--streams", "1", "--workload", "C2"]
+           "--steps", "1", "--warmup", "1", "--streams", "1", "--workload", "C2", "--cpu-single-frames", "2"]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
     assert r.returncode == 0, r.stderr[-2000:]
     lines = [l for l in r.stdout.splitlines() if l.startswith("{")]
@@ -65,3 +65,6 @@ def test_reference_arm_prints_on_rank0_only():
     d = json.loads(lines[0])
     assert d["impl"] == "reference" and d["n_gpus"] == 2 and d["value"] > 0 and d["gpu_launches"] == 0
     assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["cpu_baseline"]["kind"] in ("reference", "port")
+    cb = d["cpu_baseline"]
+    assert cb["python_overhead_frac"] < 0.02 and cb["single_sequence_1_thread"]["frames_per_s"] > 0
+    assert cb["cv2"]["getNumberOfCPUs"] >= 1 and set(cb["stage_ms_median"]) == {"lk", "mask", "detect", "convert", "bucket"}
