@@ -295,19 +295,29 @@ def run_single_stream(capi, Frontend, torch, local, wl, frames1, steps):
     return out
 
 
-def run_drop_in(wl):
-    """Config 1 through the C++ wrappers with the reference's signatures (svo_b200/host/frontend_selftest --bench)."""
+def run_drop_in(wl, frames1, n_frames=200):
+    """Config 1 through the C++ wrappers with the reference's signatures (svo_b200/host/frontend_selftest --bench): host
+    cv::Mat frames and std::vector containers in, std::vector<cv::KeyPoint> / Point2f / status / err out, every call."""
     exe = os.path.join(ROOT, "svo_b200", "lib", "frontend_selftest")
     if not os.path.exists(exe):
         return {"unavailable": "svo_b200/lib/frontend_selftest not built"}
+    path = None
     try:
-        r = subprocess.run([exe, "--bench", "200"], capture_output=True, text=True, timeout=300)
+        with tempfile.NamedTemporaryFile("wb", suffix=".bin", delete=False) as f:
+            path = f.name
+            np.array([wl["w"], wl["h"], frames1.shape[0], wl["n_tracks"], wl["bucket_size"], wl["per_bucket"], wl["fast_thr"]],
+                     np.int32).tofile(f)
+            np.ascontiguousarray(frames1).tofile(f)
+        r = subprocess.run([exe, "--bench", path, str(n_frames)], capture_output=True, text=True, timeout=300)
         for line in r.stdout.splitlines():
             if line.startswith("{"):
                 return json.loads(line)
         return {"unavailable": "no JSON line (rc %d): %s" % (r.returncode, (r.stdout + r.stderr)[-200:])}
     except Exception as e:
         return {"unavailable": repr(e)[:200]}
+    finally:
+        if path and os.path.exists(path):
+            os.unlink(path)
 
 
 def run_b200(args):
@@ -544,7 +554,7 @@ def run_b200(args):
         except Exception as e:   # an extra must never cost the headline line
             line["single_stream"] = {"error": repr(e)[:200]}
         if world == 1:
-            line["drop_in"] = run_drop_in(wl)
+            line["drop_in"] = run_drop_in(wl, np.ascontiguousarray(frames[:, 0]))
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline_block(wl, 3, args.cpu_frames, args.cpu_single_frames)
     print(json.dumps(line))

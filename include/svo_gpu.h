@@ -103,6 +103,14 @@ SVO_GPU_API int svo_gpu_download_image(svo_gpu_ctx* ctx, int slot, int lane, uin
  * cv::calcOpticalFlowPyrLK runs on both images on every call (src/tracking.cpp:101-105, :160-165); *levels_out gets the
  * effective maxLevel (construction stops when a level would be <= winSize). */
 SVO_GPU_API int svo_gpu_build_pyramid(svo_gpu_ctx* ctx, int slot, int win_w, int win_h, int max_level, int* levels_out);
+/* Pure helpers for callers that keep pyramids across calls (the wrappers' frame cache, svo_b200/host/feature.cpp):
+ * the effective maxLevel cv::buildOpticalFlowPyramid would return for this image / window / maxLevel, the margin a
+ * pyramid built for this window carries, and what `slot` holds now (*levels_out = levels built, 0 = no pyramid).
+ * svo_gpu_klt accepts any two pyramids of equal margin that hold the levels it needs: level l of an image does not
+ * depend on the window the pyramid was built for. */
+SVO_GPU_API int svo_gpu_pyramid_levels(int w, int h, int win_w, int win_h, int max_level);
+SVO_GPU_API int svo_gpu_pyramid_margin(int win_w, int win_h);
+SVO_GPU_API int svo_gpu_slot_pyramid(const svo_gpu_ctx* ctx, int slot, int* levels_out, int* margin_out);
 /* Test/debug read-back of one pyramid level of lane `lane` (tightly packed w*h bytes). */
 SVO_GPU_API int svo_gpu_download_level(svo_gpu_ctx* ctx, int slot, int lane, int level, uint8_t* host, int capacity_bytes,
                                        int* w_out, int* h_out);
@@ -118,7 +126,9 @@ SVO_GPU_API int svo_gpu_download_level_padded(svo_gpu_ctx* ctx, int slot, int la
  * cv::FastFeatureDetector::create(threshold, nonMaxSuppression) (src/tracking.cpp:54-57).
  *   mask_or_null: host CV_8UC1 mask of the image size (0 = reject), as built at src/tracking.cpp:76-79, or NULL.
  *   xy_out[2*i], xy_out[2*i+1] = KeyPoint::pt; response_out[i] = KeyPoint::response (score with NMS, 0 without).
- *   The other KeyPoint fields are constants: size 7, angle -1, octave 0, class_id -1. */
+ *   The other KeyPoint fields are constants: size 7, angle -1, octave 0, class_id -1.
+ *   Entries of xy_out / response_out beyond *count_out (up to capacity) are unspecified: the list leaves the device
+ *   together with its length, sized by the previous call's result, so that the usual call synchronises once. */
 SVO_GPU_API int svo_gpu_fast(svo_gpu_ctx* ctx, int slot, int threshold, int nms, const uint8_t* mask_or_null,
                              size_t mask_stride, float* xy_out, float* response_out, int capacity, int* count_out);
 

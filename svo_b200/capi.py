@@ -39,6 +39,9 @@ SYMBOLS = {
                                            C.c_size_t, C.c_int]),
     "svo_gpu_download_image": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_size_t]),
     "svo_gpu_build_pyramid": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, _i32p]),
+    "svo_gpu_pyramid_levels": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
+    "svo_gpu_pyramid_margin": (C.c_int, [C.c_int, C.c_int]),
+    "svo_gpu_slot_pyramid": (C.c_int, [C.c_void_p, C.c_int, _i32p, _i32p]),
     "svo_gpu_download_level": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, _i32p, _i32p]),
     "svo_gpu_download_level_padded": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, _i32p, _i32p,
                                                 _i32p]),

@@ -87,6 +87,10 @@ struct svo_gpu_ctx {
     int* flt_n = nullptr;         // [B]
     // pinned scratch for small read-backs
     int* h_small = nullptr;       // 4 * max_batch + 16 ints
+    int fetch_hint = 0;           // keypoints svo_gpu_fast last returned (+ 25 %): copied back together with the count
+    int bucket_fetch_hint = 0;    // same for svo_gpu_bucket
+    uint8_t* h_bucket = nullptr;  // pinned staging of svo_gpu_bucket's speculative read-back (bucket_stage_cap entries)
+    int bucket_stage_cap = 0;
 
     // svo_gpu_step state
     bool step_has_prev = false;
@@ -271,6 +275,8 @@ static int create_buffers(svo_gpu_ctx* ctx)
         CK(cudaMemcpy(ctx->int_max, big.data(), sizeof(int) * B, cudaMemcpyHostToDevice));
     }
     CK(cudaMallocHost(reinterpret_cast<void**>(&ctx->h_small), sizeof(int) * (4 * B + 16)));
+    ctx->bucket_stage_cap = (int)std::min<size_t>(NP, 16384);
+    CK(cudaMallocHost(reinterpret_cast<void**>(&ctx->h_bucket), (sizeof(float2) + sizeof(int)) * (size_t)ctx->bucket_stage_cap));
     for (auto& tk : ctx->tickets) {
         CK(cudaMallocHost(reinterpret_cast<void**>(&tk.hs), sizeof(int) * (4 * B + 16)));
         CK(cudaEventCreateWithFlags(&tk.done, cudaEventDisableTiming));
@@ -377,6 +383,7 @@ extern "C" int svo_gpu_destroy(svo_gpu_ctx* ctx)
                     ctx->flt_b, ctx->flt_err, ctx->flt_n};
     for (void* p : bufs) cudaFree(p);
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
+    if (ctx->h_bucket) cudaFreeHost(ctx->h_bucket);
     if (ctx->st) cudaStreamDestroy(ctx->st);
     delete ctx;
     return 0;
@@ -544,6 +551,23 @@ static int enqueue_pyramid(svo_gpu_ctx* ctx, Slot& s, int win_w, int win_h, int 
     s.pyr_built = true;
     s.win_w = win_w; s.win_h = win_h;
     if (levels_out) *levels_out = eff;
+    return 0;
+}
+
+extern "C" int svo_gpu_pyramid_levels(int w, int h, int win_w, int win_h, int max_level)
+{
+    if (w < 1 || h < 1 || win_w < 1 || win_h < 1 || max_level < 0) return 0;
+    return effective_levels(w, h, win_w, win_h, std::min(max_level, SVO_GPU_MAX_LEVELS - 1));
+}
+
+extern "C" int svo_gpu_pyramid_margin(int win_w, int win_h) { return margin_for(win_w, win_h); }
+
+extern "C" int svo_gpu_slot_pyramid(const svo_gpu_ctx* ctx, int slot, int* levels_out, int* margin_out)
+{
+    if (!ctx || slot < 0 || slot >= SVO_GPU_NUM_SLOTS) return SVO_GPU_E_ARG;
+    const Slot& s = ctx->slots[slot];
+    if (levels_out) *levels_out = s.pyr_built ? s.g.nlevels : 0;
+    if (margin_out) *margin_out = s.pyr_built ? s.g.P : 0;
     return 0;
 }
 

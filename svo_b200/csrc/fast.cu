@@ -87,11 +87,14 @@ __device__ __forceinline__ uint32_t packed_best(const uint32_t (&D)[16])
 template <int NT>
 __global__ void __launch_bounds__(NT) fast_tile_kernel(const uint8_t* __restrict__ raw, size_t raw_pitch, size_t raw_lane,
                                                        int w, int h, int t, int nms, const uint8_t* __restrict__ mask,
-                                                       size_t mask_pitch, size_t mask_lane, FastBufs fb, int ntx)
+                                                       size_t mask_pitch, size_t mask_lane, FastBufs fb, int ntx,
+                                                       FastMaskPts mp)
 {
     __shared__ __align__(16) uint32_t simg_pad[RH * RWW + 2];   // one pad word on each side: ring_word reads words g-1, g+1
     __shared__ __align__(16) uint32_t sbest_pad[SH * RWW + 2];  // excess of the score over the threshold, one byte per pixel,
                                                                 // same column layout as the staged image (0 = no corner)
+    // mask given as points (src/tracking.cpp:76-79): bit x of word (row, x / 32) = mask pixel of tile pixel (x, row) != 0
+    __shared__ uint32_t smask[TH * (TW / 32)];
     uint32_t* simg = simg_pad + 1;
     uint32_t* sbest = sbest_pad + 1;
     const int tid = threadIdx.x;
@@ -100,6 +103,8 @@ __global__ void __launch_bounds__(NT) fast_tile_kernel(const uint8_t* __restrict
     const uint8_t* src = raw + (size_t)lane_id * raw_lane;
 
     if (tid == 0) { simg_pad[0] = 0; simg_pad[RH * RWW + 1] = 0; sbest_pad[0] = 0; sbest_pad[SH * RWW + 1] = 0; }
+    if (mp.pts)
+        for (int i = tid; i < TH * (TW / 32); i += NT) smask[i] = 0xffffffffu;
 
     // ---- stage the (TW+8) x (TH+8) region; coordinates are clamped to the image (clamped pixels are never used by a
     //      valid candidate: those sit at least 3 px inside the image)
@@ -122,6 +127,28 @@ __global__ void __launch_bounds__(NT) fast_tile_kernel(const uint8_t* __restrict
         simg[i] = v;
     }
     __syncthreads();
+
+    // ---- the tile's part of the reference's mask, straight from the points it is drawn around: every thread walks its share
+    //      of the lane's points and clears the bits of the boxes that reach into this tile (the full-frame mask plane,
+    //      its 255-fill and the box kernel are never materialised).  Box = [cvRound(x - half), cvRound(x + half)] x
+    //      [cvRound(y - half), cvRound(y + half)], float subtraction first, round half to even (cv::Point2f -> cv::Point).
+    if (mp.pts) {
+        const int n = min(mp.n_dev[lane_id], mp.n_max);
+        const float2* pts = mp.pts + (size_t)lane_id * mp.pts_lane;
+        for (int i = tid; i < n; i += NT) {
+            const float2 p = __ldg(pts + i);
+            // clamped to the tile before the tile origin is subtracted (the conversions saturate at INT_MIN / INT_MAX)
+            const int ya = max(__float2int_rn(__fsub_rn(p.y, mp.half)), y0) - y0, yb = min(__float2int_rn(__fadd_rn(p.y, mp.half)), y0 + TH - 1) - y0;
+            if (ya > yb) continue;
+            const int xa = max(__float2int_rn(__fsub_rn(p.x, mp.half)), x0) - x0, xb = min(__float2int_rn(__fadd_rn(p.x, mp.half)), x0 + TW - 1) - x0;
+            if (xa > xb) continue;
+            for (int wd = xa >> 5; wd <= xb >> 5; ++wd) {
+                const int lo = max(xa - 32 * wd, 0), hi = min(xb - 32 * wd, 31);
+                const uint32_t clr = ~((0xffffffffu >> (31 - hi)) & (0xffffffffu << lo));
+                for (int y = ya; y <= yb; ++y) atomicAnd(&smask[y * (TW / 32) + wd], clr);
+            }
+        }
+    }
 
     // ---- pass 1: dense packed corner score of every 4-pixel group of the score region (rows y0-1 .. y0+TH, staged
     //      columns 0 .. RW-1): sbest byte = max(best - t, 0), where best = cornerScore + 1.
@@ -207,6 +234,7 @@ __global__ void __launch_bounds__(NT) fast_tile_kernel(const uint8_t* __restrict
             // keep <=> s > m <=> (s + 0x7fff) - m has bit 15 set (fields stay inside [0x7f00, 0x80fe])
             const uint32_t ke = (even_px(wc) + 0x7fff7fffu) - me, ko = (odd_px(wc) + 0x7fff7fffu) - mo;
             bits = ((ke >> 15) & 1u) | ((ko >> 14) & 2u) | ((ke >> 29) & 4u) | ((ko >> 28) & 8u);
+            if (bits && mp.pts) bits &= smask[r * (TW / 32) + (ln >> 3)] >> (4 * (ln & 7));
             if (bits && mask) {
                 const uint8_t* mrow = mask + (size_t)lane_id * mask_lane + (size_t)gy * mask_pitch + x0 + 4 * ln;
 #pragma unroll
@@ -289,31 +317,13 @@ __global__ void __launch_bounds__(kGatherRows * 32) fast_gather_kernel(int w, in
     }
 }
 
-// one warp per point: zero the rounded inclusive box (src/tracking.cpp:76-79)
-__global__ void __launch_bounds__(128) mask_boxes_kernel(uint8_t* __restrict__ mask, size_t mask_pitch, size_t mask_lane,
-                                                         int w, int h, const float2* __restrict__ pts, size_t pts_lane,
-                                                         const int* __restrict__ n_dev, int n_max, float half)
-{
-    const int lane_id = blockIdx.y;
-    const int i = blockIdx.x * 4 + (threadIdx.x >> 5);
-    const int n = min(n_dev[lane_id], n_max);
-    if (i >= n) return;
-    const float2 p = pts[(size_t)lane_id * pts_lane + i];
-    // float subtraction first, then cv::Point2f -> cv::Point (saturate_cast<int> = round half to even)
-    int xa = __float2int_rn(__fsub_rn(p.x, half)), xb = __float2int_rn(__fadd_rn(p.x, half));
-    int ya = __float2int_rn(__fsub_rn(p.y, half)), yb = __float2int_rn(__fadd_rn(p.y, half));
-    xa = max(xa, 0); ya = max(ya, 0); xb = min(xb, w - 1); yb = min(yb, h - 1);
-    uint8_t* m = mask + (size_t)lane_id * mask_lane;
-    for (int y = ya; y <= yb; ++y)
-        for (int x = xa + (int)(threadIdx.x & 31); x <= xb; x += 32) m[(size_t)y * mask_pitch + x] = 0;
-}
-
 }  // namespace
 
 void launch_fast(cudaStream_t st, const uint8_t* raw, size_t raw_pitch, size_t raw_lane, int w, int h, int threshold,
                  int nms, const uint8_t* mask, size_t mask_pitch, size_t mask_lane, const FastBufs& fb, int batch,
-                 long long* launches, int small_ctas)
+                 long long* launches, int small_ctas, const FastMaskPts* mask_pts)
 {
+    const FastMaskPts mp = mask_pts && mask_pts->pts && mask_pts->n_max > 0 ? *mask_pts : FastMaskPts{};
     threshold = threshold < 0 ? 0 : (threshold > 255 ? 255 : threshold);
     cudaMemsetAsync(fb.rowtotal, 0, sizeof(int) * (size_t)fb.rows_cap * batch, st);
     if (w < 7 || h < 7) {   // no candidate pixel at all (OpenCV returns an empty list)
@@ -328,26 +338,12 @@ void launch_fast(cudaStream_t st, const uint8_t* raw, size_t raw_pitch, size_t r
     dim3 grid(ntx, (h + TH - 1) / TH, batch);
     if (small_ctas)   // the default: 128-thread CTAs measured 2 % faster than 256 (and 64 slower), gpurun_out/s11, s12
         fast_tile_kernel<128><<<grid, 128, 0, st>>>(raw, raw_pitch, raw_lane, w, h, threshold, nms, mask, mask_pitch, mask_lane,
-                                                    fb, ntx);
+                                                    fb, ntx, mp);
     else
         fast_tile_kernel<256><<<grid, 256, 0, st>>>(raw, raw_pitch, raw_lane, w, h, threshold, nms, mask, mask_pitch, mask_lane,
-                                                    fb, ntx);
+                                                    fb, ntx, mp);
     fast_gather_kernel<<<dim3((h + kGatherRows - 1) / kGatherRows, batch), kGatherRows * 32, 0, st>>>(w, h, threshold, nms, fb, ntx);
     if (launches) *launches += 2;
-}
-
-void launch_build_mask(cudaStream_t st, uint8_t* mask, size_t mask_pitch, size_t mask_lane, int w, int h,
-                       const float2* pts, size_t pts_lane, const int* n_dev, int n_max, float half, int batch,
-                       long long* launches)
-{
-    // one fill for all lanes (lanes are mask_lane apart and the padding of a lane is never read)
-    cudaMemsetAsync(mask, 255, (size_t)(batch - 1) * mask_lane + (size_t)(h - 1) * mask_pitch + (size_t)w, st);
-    if (n_max <= 0) return;
-    static std::atomic<unsigned long long> seen{0};
-    if (first_on_device(seen)) prefer_max_shared(mask_boxes_kernel);
-    mask_boxes_kernel<<<dim3((n_max + 3) / 4, batch), 128, 0, st>>>(mask, mask_pitch, mask_lane, w, h, pts, pts_lane,
-                                                                  n_dev, n_max, half);
-    if (launches) ++*launches;
 }
 
 }  // namespace svo

@@ -83,15 +83,21 @@ struct FastBufs {
     int kp_cap;
 };
 
-// mask: device u8 plane per lane (pitch mask_pitch, lane stride mask_lane) or nullptr
+// The reference's mask given by the points it is drawn around (src/tracking.cpp:76-79: 255 everywhere, 0 in the rounded
+// inclusive box of +-half px around each point): evaluated per tile inside the FAST kernel, never materialised.
+// pts: [B][pts_lane] float2, n per lane = min(n_dev[lane], n_max); pts == nullptr or n_max <= 0: no mask.
+struct FastMaskPts {
+    const float2* pts = nullptr;
+    size_t pts_lane = 0;
+    const int* n_dev = nullptr;
+    int n_max = 0;
+    float half = 0.f;
+};
+
+// mask: device u8 plane per lane (pitch mask_pitch, lane stride mask_lane) or nullptr; mask_pts: see above (either, or none)
 void launch_fast(cudaStream_t st, const uint8_t* raw, size_t raw_pitch, size_t raw_lane, int w, int h, int threshold,
                  int nms, const uint8_t* mask, size_t mask_pitch, size_t mask_lane, const FastBufs& fb, int batch,
-                 long long* launches, int small_ctas = 1);
-// mask plane = 255, then 0 in the rounded inclusive box around each point (src/tracking.cpp:76-79)
-// pts: [B][pts_lane] float2, n per lane from n_dev[lane] (device) clamped to n_max
-void launch_build_mask(cudaStream_t st, uint8_t* mask, size_t mask_pitch, size_t mask_lane, int w, int h,
-                       const float2* pts, size_t pts_lane, const int* n_dev, int n_max, float half, int batch,
-                       long long* launches);
+                 long long* launches, int small_ctas = 1, const FastMaskPts* mask_pts = nullptr);
 
 // ------------------------------------------------------------------------------------------------ bucket.cu
 struct BucketBufs {

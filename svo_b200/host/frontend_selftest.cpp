@@ -6,7 +6,9 @@
 //   Tracking::trackFrames            src/tracking.cpp:154-179 LK 21x21, 50 it, OPTFLOW_LK_GET_MIN_EIGENVALS
 // usage: frontend_selftest <in.bin> <out.bin>     in.bin = int32 {w, h, n_prev, bucket_size, per_bucket}, image a, image b,
 //                                                  n_prev x float2 previously tracked points
+//        frontend_selftest --bench <frames.bin> <n_frames>   one sequence through the wrappers, timed (see bench_main)
 // Without a CUDA device every call must throw (no CPU fallback): `frontend_selftest --expect-no-gpu` checks exactly that.
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -24,12 +26,131 @@ static void fill_box(cv::Mat& m, cv::Point2f a, cv::Point2f b)   // cv::rectangl
     int xa = rnd(a.x), ya = rnd(a.y), xb = rnd(b.x), yb = rnd(b.y);
     xa = xa < 0 ? 0 : xa; ya = ya < 0 ? 0 : ya;
     xb = xb >= m.cols ? m.cols - 1 : xb; yb = yb >= m.rows ? m.rows - 1 : yb;
-    for (int y = ya; y <= yb; ++y)
-        for (int x = xa; x <= xb; ++x) m.at<uchar>(y, x) = 0;
+    if (xa > xb) return;
+    for (int y = ya; y <= yb; ++y) memset(m.ptr<uchar>(y) + xa, 0, (size_t)(xb - xa + 1));   // row fills, as cv::rectangle does
+}
+
+// BASELINE config 1 through the drop-in wrappers: ONE 1241x376 sequence, the loop body of Tracking::startStereo on a
+// key-frame (src/tracking.cpp:240-257) written with the reference's own calls and host containers:
+//   svo::calcOpticalFlowPyrLK(prev, cur, tracks, ...)  (:160-165)   host cv::Mat frames, std::vector<cv::Point2f> tracks
+//   mask of +-10 px boxes on the host (:76-79)  ->  mDetector->detect(cur, keypoints, mask)  (:82)  ->  KeyPoint::convert (:86)
+//   FeatureSet::appendNewFeatures + bucketingFeatures  (:88)  ->  the first max_tracks features are the next frame's tracks
+// Pass "host_mask": exactly that (the three-identifier patch of INTEGRATION.md; the w*h mask crosses PCIe every frame).
+// Pass "device_mask": detect replaced by svo::detectFASTAvoiding(cur, tracks, 10, ...) (one more changed line).
+// frames.bin = int32 {w, h, ring, max_tracks, bucket_size, per_bucket, fast_threshold} + ring images; frame t = image t % ring
+// with its first two pixels stamped with t, so that every frame is new to the wrappers' frame cache, as camera frames are.
+static int bench_main(const char* path, int n_frames)
+{
+    using clk = std::chrono::steady_clock;
+    auto ms = [](clk::time_point a, clk::time_point b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+    FILE* fi = fopen(path, "rb");
+    if (!fi) return 2;
+    int hdr[7];
+    if (fread(hdr, sizeof(int), 7, fi) != 7) return 2;
+    const int w = hdr[0], h = hdr[1], ring = hdr[2], max_tracks = hdr[3], bs = hdr[4], k = hdr[5], thr = hdr[6];
+    std::vector<cv::Mat> src((size_t)ring);
+    for (auto& m : src) {
+        m.create(h, w, CV_8UC1);
+        if (fread(m.data, 1, (size_t)w * h, fi) != (size_t)w * h) return 2;
+    }
+    fclose(fi);
+    try {
+        cv::Ptr<cv::FeatureDetector> mDetector = svo::GpuFastDetector::create(thr, true);
+        const cv::TermCriteria tc(cv::TermCriteria::COUNT + cv::TermCriteria::EPS, 50, 0.001);
+        printf("{\"workload\": \"one %dx%d sequence, %d tracks, mask + FAST %d + NMS, bucketing %d/%d, LK 21x21 4 levels 50 it\", \"frames\": %d",
+               w, h, max_tracks, thr, bs, k, n_frames);
+        for (int pass = 0; pass < 2; ++pass) {
+            const bool device_mask = pass == 1;
+            double t_lk = 0, t_mask = 0, t_det = 0, t_conv = 0, t_bucket = 0, t_all = 0;
+            long long ok = 0, ntr = 0, nkp = 0;
+            std::vector<cv::Point2f> tracks, nextPts, newPoints;
+            std::vector<uchar> status;
+            std::vector<cv::KeyPoint> keypoints;
+            cv::Mat error, prev;
+            FeatureSet fs;
+            const svo::FrameCacheStats c0 = svo::frameCacheStats();
+            long long launches0 = 0;
+            const int warm = 10;
+            for (int t = 0; t < warm + n_frames; ++t) {
+                cv::Mat cur(h, w, CV_8UC1);                      // what the loader hands over: a new frame in its own buffer
+                memcpy(cur.data, src[(size_t)(t % ring)].data, (size_t)w * h);
+                const int stamp = pass * 100000 + t;
+                cur.data[0] = (uchar)(stamp & 255); cur.data[1] = (uchar)((stamp >> 8) & 255); cur.data[2] = (uchar)(stamp >> 16);
+                if (t == warm) {
+                    t_lk = t_mask = t_det = t_conv = t_bucket = t_all = 0;
+                    ok = ntr = nkp = 0;
+                    launches0 = svo_gpu_launch_count(svo::defaultContext(svo::currentDevice()));
+                }
+                const auto a0 = clk::now();
+                if (!prev.empty() && !tracks.empty()) {
+                    svo::calcOpticalFlowPyrLK(prev, cur, tracks, nextPts, status, error, cv::Size(21, 21), 3, tc,
+                                              cv::OPTFLOW_LK_GET_MIN_EIGENVALS);
+                    for (uchar s : status) ok += s;
+                    ntr += (long long)status.size();
+                }
+                const auto a1 = clk::now();
+                auto a2 = a1;
+                if (device_mask) {
+                    svo::detectFASTAvoiding(cur, tracks, 10.f, keypoints, thr, true);
+                } else {
+                    cv::Mat mask(cur.size(), CV_8UC1, 255);
+                    for (const auto& p : tracks) fill_box(mask, p - cv::Point2f(10, 10), p + cv::Point2f(10, 10));
+                    a2 = clk::now();
+                    mDetector->detect(cur, keypoints, mask);
+                }
+                const auto a3 = clk::now();
+                cv::KeyPoint::convert(keypoints, newPoints);
+                const auto a4 = clk::now();
+                fs.clear();
+                fs.appendNewFeatures(newPoints);
+                fs.bucketingFeatures(cur, bs, k);
+                tracks.assign(fs.points.begin(), fs.points.begin() + std::min<size_t>(fs.points.size(), (size_t)max_tracks));
+                const auto a5 = clk::now();
+                prev = cur;
+                nkp += (long long)keypoints.size();
+                t_lk += ms(a0, a1); t_mask += ms(a1, a2); t_det += ms(a2, a3); t_conv += ms(a3, a4); t_bucket += ms(a4, a5);
+                t_all += ms(a0, a5);
+            }
+            const svo::FrameCacheStats c1 = svo::frameCacheStats();
+            const long long launches = svo_gpu_launch_count(svo::defaultContext(svo::currentDevice())) - launches0;
+            const double n = n_frames;
+            printf(", \"%s\": {\"ms_per_frame\": %.4f, \"frames_per_s\": %.1f, \"stage_ms\": {\"lk\": %.4f, \"mask_host\": %.4f, "
+                   "\"detect\": %.4f, \"convert\": %.4f, \"bucket\": %.4f}, \"tracks_per_frame\": %.1f, \"status_ok_frac\": %.5f, "
+                   "\"keypoints_per_frame\": %.1f, \"launches_per_frame\": %.2f, \"cache\": {\"hits\": %lld, \"uploads\": %lld, "
+                   "\"pyramids\": %lld}}",
+                   device_mask ? "device_mask" : "host_mask", t_all / n, 1e3 * n / t_all, t_lk / n, t_mask / n, t_det / n, t_conv / n,
+                   t_bucket / n, ntr / n, ntr ? (double)ok / (double)ntr : 0., nkp / n, launches / n, c1.hits - c0.hits,
+                   c1.uploads - c0.uploads, c1.pyramids - c0.pyramids);
+        }
+        // the same frame pair again: no upload, no pyramid, exactly one launch (the LK kernel)
+        {
+            cv::Mat a = src[0], b = src[1 % ring];
+            std::vector<cv::Point2f> pts(100), out;
+            for (int i = 0; i < 100; ++i) pts[(size_t)i] = cv::Point2f(40.f + 7.f * i, 50.f + (i % 9) * 20.f);
+            std::vector<uchar> st;
+            cv::Mat er;
+            svo::calcOpticalFlowPyrLK(a, b, pts, out, st, er, cv::Size(21, 21), 3, tc, cv::OPTFLOW_LK_GET_MIN_EIGENVALS);
+            const svo::FrameCacheStats c0 = svo::frameCacheStats();
+            const long long l0 = svo_gpu_launch_count(svo::defaultContext(svo::currentDevice()));
+            svo::calcOpticalFlowPyrLK(a, b, pts, out, st, er, cv::Size(21, 21), 3, tc, cv::OPTFLOW_LK_GET_MIN_EIGENVALS);
+            svo::calcOpticalFlowPyrLK(a, b, pts, out, st, er, cv::Size(11, 11), 3, tc);   // the stereo window on the same pyramids
+            const svo::FrameCacheStats c1 = svo::frameCacheStats();
+            printf(", \"repeat_call\": {\"launches\": %lld, \"uploads\": %lld, \"pyramids\": %lld, \"hits\": %lld}",
+                   svo_gpu_launch_count(svo::defaultContext(svo::currentDevice())) - l0, c1.uploads - c0.uploads,
+                   c1.pyramids - c0.pyramids, c1.hits - c0.hits);
+        }
+        printf("}\n");
+    } catch (const cv::Exception& e) {
+        fprintf(stderr, "frontend_selftest --bench: %s\n", e.what());
+        return 1;
+    }
+    svo::releaseContexts();
+    return 0;
 }
 
 int main(int argc, char** argv)
 {
+    if (argc == 4 && !strcmp(argv[1], "--bench")) return bench_main(argv[2], atoi(argv[3]));
     if (argc == 2 && !strcmp(argv[1], "--expect-no-gpu")) {
         cv::Mat img(cv::Size(64, 64), CV_8UC1, 7);
         std::vector<cv::KeyPoint> kps;

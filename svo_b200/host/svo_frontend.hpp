@@ -44,6 +44,19 @@ int currentDevice();
 // Releases this thread's contexts (otherwise released at thread exit).
 void releaseContexts();
 
+// Frame cache of the wrappers below.  The reference passes plain cv::Mat images, so cv::calcOpticalFlowPyrLK rebuilds both
+// pyramids on every call: a frame's pyramid is built as `next` (src/tracking.cpp:160-165), again as `prev` of the following
+// frame, and a third time for the stereo call on a key-frame (:101-105).  The wrappers keep the last SVO_GPU_NUM_SLOTS
+// frames on the device, recognised by CONTENT (size, type, 64-bit checksum of the pixels; a deep copy hits, a recycled buffer
+// with new pixels cannot), so each frame is uploaded and its pyramid built once.  Results are identical either way.
+void setFrameCache(bool enabled);   // default: enabled; per thread
+struct FrameCacheStats {
+    long long hits = 0;       // image arguments found on the device
+    long long uploads = 0;    // image arguments copied to the device
+    long long pyramids = 0;   // pyramid builds
+};
+FrameCacheStats frameCacheStats();   // of the calling thread's context on its current device
+
 // cv::FastFeatureDetector stand-in: FAST-9/16, threshold, optional 3x3 NMS, optional mask; keypoints in raster order with
 // size 7, angle -1, response = score, octave 0, class_id -1, exactly as cv::FastFeatureDetector::detect returns them.
 class GpuFastDetector : public cv::Feature2D {

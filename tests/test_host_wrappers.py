@@ -146,3 +146,29 @@ def test_wrappers_match_oracle(exe, oracle, tmp_path):
     assert int(take(np.int32, 1)[0]) == 1
     assert int(take(np.int32, 1)[0]) == len(oracle.orc_fast(gray, 20, True)[0])
     assert off == len(buf)
+
+
+@pytest.mark.gpu
+def test_frame_cache_uploads_and_builds_each_frame_once(exe, tmp_path):
+    """The wrappers' content-addressed frame cache (svo_b200/host/feature.cpp): through the reference-shaped loop
+    (LK prev->cur, detect(cur, mask), bucketing) every frame is uploaded once and its pyramid built once, although it is an
+    argument of three calls (next of LK, detect, prev of the following LK: src/tracking.cpp:160-165, :82); a repeated LK call
+    on the same pair -- also with the stereo window -- launches the LK kernel and nothing else."""
+    import json
+    w, h, ring, n = 320, 240, 4, 6
+    seq = synth.sequence(w, h, 9, ring)
+    fin = tmp_path / "frames.bin"
+    with open(fin, "wb") as f:
+        np.array([w, h, ring, 300, 32, 5, 20], np.int32).tofile(f)
+        seq.tofile(f)
+    r = subprocess.run([exe, "--bench", str(fin), str(n)], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    d = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][0])
+    total = n + 10                                         # warm-up frames included in the cache counters
+    for mode in ("host_mask", "device_mask"):
+        c = d[mode]["cache"]
+        assert c["uploads"] == total and c["pyramids"] == total and c["hits"] == 2 * (total - 1), (mode, c)
+        assert d[mode]["tracks_per_frame"] > 100 and d[mode]["status_ok_frac"] > 0.9
+    assert d["host_mask"]["keypoints_per_frame"] == d["device_mask"]["keypoints_per_frame"]
+    rep = d["repeat_call"]
+    assert rep == {"launches": 2, "uploads": 0, "pyramids": 0, "hits": 4}, rep
