@@ -107,17 +107,16 @@ struct svo_gpu_ctx {
     cudaEvent_t ev_copy = nullptr;
     cudaStream_t out_st = nullptr;     // LK results go back to the host on this stream while FAST and bucketing still run
     cudaEvent_t ev_klt = nullptr, ev_out = nullptr;
-    // detection beside tracking: mask, FAST and bucketing run on aux_st while the LK kernel keeps klt_reserve CTA slots per
-    // SM free for them; a helper launch of the LK kernel on aux_st takes those slots over afterwards (same work queue)
+    // detection beside tracking: FAST and bucketing run on aux_st while the LK kernel runs on st (small batches, see capi_step.inc)
     cudaStream_t aux_st = nullptr;
     // the step builds the new frame's pyramid on pyr_st (highest priority): with a step still in flight it runs beside that
     // step's FAST and bucketing, as soon as that step's LK no longer needs the slot's previous pyramid
     cudaStream_t pyr_st = nullptr;
     cudaEvent_t ev_pyr = nullptr;
     int pyr_async = 1;      // SVO_GPU_STEP_PYR_ASYNC (0 = pyramid on the main stream)
+    int pyr_fused = 1;      // SVO_GPU_PYR_FUSED (0 = ingest + one pyrDown launch per level)
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
-    int overlap = 0;        // SVO_GPU_STEP_OVERLAP (0 = one stream, stages back to back; 1 measured slower, gpurun_out/s6)
-    int klt_reserve = 3;    // SVO_GPU_KLT_RESERVE
+    int overlap = -1;       // SVO_GPU_STEP_OVERLAP: -1 = per call (detection beside LK when LK does not fill the device), 0 / 1 = never / always
     int fast_small = 1;     // SVO_GPU_FAST_SMALL: 128-thread FAST CTAs in the step (0 = 256)
     const uint8_t* pf_ptr = nullptr;   // host pointer of the prefetched frames (nullptr = none pending)
     int pf_slot = -1;
@@ -304,9 +303,9 @@ static int create_buffers(svo_gpu_ctx* ctx)
         CK(cudaEventCreateWithFlags(&ctx->ev_pyr, cudaEventDisableTiming));
     }
     if (const char* v = getenv("SVO_GPU_STEP_PYR_ASYNC")) ctx->pyr_async = atoi(v);
+    if (const char* v = getenv("SVO_GPU_PYR_FUSED")) ctx->pyr_fused = atoi(v);
     if (const char* v = getenv("SVO_GPU_BUCKET_MODE")) ctx->bb.mode = atoi(v);   // 1: global-memory kernels, 2: one CTA per lane
     if (const char* v = getenv("SVO_GPU_STEP_OVERLAP")) ctx->overlap = atoi(v);
-    if (const char* v = getenv("SVO_GPU_KLT_RESERVE")) ctx->klt_reserve = atoi(v);
     if (const char* v = getenv("SVO_GPU_FAST_SMALL")) ctx->fast_small = atoi(v);
     CK(cudaStreamSynchronize(ctx->st));
     return 0;
@@ -545,8 +544,12 @@ static int enqueue_pyramid(svo_gpu_ctx* ctx, Slot& s, int win_w, int win_h, int 
     make_geometry(s.g, s.w, s.h, eff + 1, margin_for(win_w, win_h));
     if (int r = ensure(ctx, s.pyr, (size_t)s.g.lane_bytes * (size_t)ctx->max_batch)) return r;
     uint8_t* pyr = static_cast<uint8_t*>(s.pyr.p);
-    launch_ingest(ps, s.raw, s.raw_pitch, s.raw_lane, pyr, s.g, s.batch, &ctx->launches);
-    for (int l = 1; l <= eff; ++l) launch_pyrdown(ps, pyr, s.g, l, s.batch, &ctx->launches);
+    int built = ctx->pyr_fused ? launch_pyramid_fused(ps, s.raw, s.raw_pitch, s.raw_lane, pyr, s.g, s.batch, &ctx->launches) : 0;
+    if (built == 0) {
+        launch_ingest(ps, s.raw, s.raw_pitch, s.raw_lane, pyr, s.g, s.batch, &ctx->launches);
+        built = 1;
+    }
+    for (int l = built; l <= eff; ++l) launch_pyrdown(ps, pyr, s.g, l, s.batch, &ctx->launches);
     CK(cudaGetLastError());
     s.pyr_built = true;
     s.win_w = win_w; s.win_h = win_h;

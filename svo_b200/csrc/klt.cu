@@ -597,11 +597,9 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) klt_run_kernel(const KltArgs
     if (lane == 0 && a.iters) atomicAdd(a.iters, iters_cta);
 }
 
-// part: kKltAll = one launch with every resident CTA slot; kKltMain / kKltHelper = the same work queue served by two
-// launches (MINB - reserve and reserve CTAs per SM), so that another kernel can use the reserved share of the SMs while
-// the main launch runs and the helper takes it over afterwards.  Only kKltAll zeroes the hand-out counter.
+// One launch with every resident CTA slot of the device (or one CTA per track when there are fewer tracks).
 template <int WW, int WH, int WARPS, bool PACKG, int MINB>
-bool launch_run(cudaStream_t st, const KltArgs& a, int batch, int part, int reserve)
+void launch_run(cudaStream_t st, const KltArgs& a, int batch)
 {
     static std::atomic<unsigned long long> seen{0};
     int dev = 0, sms = 0;
@@ -609,15 +607,11 @@ bool launch_run(cudaStream_t st, const KltArgs& a, int batch, int part, int rese
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     // every kernel that may share an SM with this one asks for the same (largest) shared-memory carve-out
     if (first_on_device(seen)) prefer_max_shared(klt_run_kernel<WW, WH, WARPS, PACKG, MINB>);
-    reserve = std::max(0, std::min(reserve, MINB - 1));
-    const int per_sm = part == kKltAll ? MINB : part == kKltMain ? MINB - reserve : reserve;
-    if (per_sm <= 0) return false;
     const long long total = (long long)a.n_max * batch;
-    dim3 grid((unsigned)std::min<long long>(total, (long long)sms * per_sm), batch);
+    dim3 grid((unsigned)std::min<long long>(total, (long long)sms * MINB), batch);
     grid.x = (grid.x + batch - 1) / batch;   // gridDim.y = batch only tells the kernel the batch size
-    if (part == kKltAll) cudaMemsetAsync(a.work, 0, sizeof(unsigned), st);
+    cudaMemsetAsync(a.work, 0, sizeof(unsigned), st);
     klt_run_kernel<WW, WH, WARPS, PACKG, MINB><<<grid, WARPS * 32, 0, st>>>(a);
-    return true;
 }
 
 // tuning knobs of the 21x21 instantiation (warps per CTA, packed gradients, minimum CTAs per SM -> register cap)
@@ -642,18 +636,24 @@ bool launch_run(cudaStream_t st, const KltArgs& a, int batch, int part, int rese
 
 }  // namespace
 
-void klt_zero_work(cudaStream_t st, const KltArgs& a) { cudaMemsetAsync(a.work, 0, sizeof(unsigned), st); }
+int klt_resident_tracks(int win_w, int win_h)
+{
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int minb = (win_w == 21 && win_h == 21) ? KLT21_MINB : (win_w == 11 && win_h == 11) ? KLT11_MINB
+                   : (win_w == 31 && win_h == 31) ? KLT31_MINB : 16;
+    return sms * minb;
+}
 
-void launch_klt(cudaStream_t st, const KltArgs& a, int batch, long long* launches, int part, int reserve)
+void launch_klt(cudaStream_t st, const KltArgs& a, int batch, long long* launches)
 {
     if (a.n_max <= 0) return;
-    bool launched = true;
-    if (a.win_w == 21 && a.win_h == 21) launched = launch_run<21, 21, KLT21_WARPS, KLT21_PACKG, KLT21_MINB>(st, a, batch, part, reserve);
-    else if (a.win_w == 11 && a.win_h == 11) launched = launch_run<11, 11, 1, false, KLT11_MINB>(st, a, batch, part, reserve);
-    else if (a.win_w == 31 && a.win_h == 31) launched = launch_run<31, 31, 1, KLT31_PACKG, KLT31_MINB>(st, a, batch, part, reserve);
-    else if (part != kKltHelper) launch_klt_generic(st, a, batch);   // not persistent: the main launch is the whole job
-    else launched = false;
-    if (launches && launched) ++*launches;
+    if (a.win_w == 21 && a.win_h == 21) launch_run<21, 21, KLT21_WARPS, KLT21_PACKG, KLT21_MINB>(st, a, batch);
+    else if (a.win_w == 11 && a.win_h == 11) launch_run<11, 11, 1, false, KLT11_MINB>(st, a, batch);
+    else if (a.win_w == 31 && a.win_h == 31) launch_run<31, 31, 1, KLT31_PACKG, KLT31_MINB>(st, a, batch);
+    else launch_klt_generic(st, a, batch);
+    if (launches) ++*launches;
 }
 
 }  // namespace svo

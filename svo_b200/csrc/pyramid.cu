@@ -174,6 +174,180 @@ __global__ void __launch_bounds__(256) pyrdown_kernel(uint8_t* __restrict__ pyr,
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// Fused build of levels 0 .. NL-1 (NL <= 4) in ONE launch: a CTA owns a 64x64 tile of level 0 and the 32x32 / 16x16 / 8x8
+// tiles of levels 1 / 2 / 3 below it.  It stages the tile of the raw frame with the halo the whole chain needs (14 px left /
+// top, 7 px right / bottom for four levels: 85x85 bytes, BORDER_REFLECT_101 applied while loading), writes its part of the
+// padded level 0, and produces each further level from the previous one in shared memory (same DP4A formulation as
+// pyrdown_kernel), writing the owned tile of every level together with the margin positions that reflect onto it.  Replaces
+// ingest_kernel + ingest_edge_kernel + up to three pyrdown_kernel launches: the raw frame is read once (plus halo, from L2),
+// every level is written once, and the five dependent sub-wave launches of a frame become one.
+// Halo slots that lie outside a level hold that level's BORDER_REFLECT_101 value: computing them like inside pixels is only
+// right when the level's width is odd, so they are overwritten with the value of the inside pixel they mirror.
+// ---------------------------------------------------------------------------------------------------------------
+struct FusedPyrArgs {
+    const uint8_t* raw;
+    size_t raw_pitch, raw_lane;
+    uint8_t* pyr;
+    long long lane_bytes;
+    LevelGeom lv[4];
+    int P;
+};
+
+constexpr int kFT = 64;   // level-0 tile edge of the fused kernel
+
+template <int NL>
+struct FusedGeo {
+    // halo of level l: left / top HL, right / bottom HR (level l+1's region [a, b] needs [2a - 2, 2b + 2] of level l)
+    __host__ __device__ static constexpr int hl(int l) { return l >= NL - 1 ? 0 : 2 * hl(l + 1) + 2; }
+    __host__ __device__ static constexpr int hr(int l) { return l >= NL - 1 ? 0 : 2 * hr(l + 1) + 1; }
+    __host__ __device__ static constexpr int n(int l) { return kFT >> l; }
+    __host__ __device__ static constexpr int rw(int l) { return n(l) + hl(l) + hr(l); }                  // region edge (square)
+    __host__ __device__ static constexpr int rq(int l) { return (rw(l) + 3) / 4; }                       // output quads per region row
+    // row pitch in bytes: the rounded-up quads of this level, and the words the next level's last quad reads
+    __host__ __device__ static constexpr int pb(int l) { return l >= NL - 1 ? 4 * rq(l) : (4 * rq(l) > 8 * rq(l + 1) + 4 ? 4 * rq(l) : 8 * rq(l + 1) + 4); }
+    __host__ __device__ static constexpr int words(int l) { return rw(l) * pb(l) / 4; }
+    __host__ __device__ static constexpr int off(int l) { return l == 0 ? 0 : off(l - 1) + words(l - 1); }
+    static constexpr int total_words = off(NL - 1) + words(NL - 1);
+};
+
+// owned tile of level D (n x n, origin (x0, y0)) from its shared-memory region -> the padded level in global memory, every
+// pixel also at the margin positions that mirror it (the usual case of pyrdown_kernel: margin narrower than the level)
+template <int N, int HL, int PB>
+__device__ __forceinline__ void fused_emit(const uint32_t* __restrict__ S, uint8_t* __restrict__ lv, const LevelGeom D, int P,
+                                           int x0, int y0, int tid)
+{
+    constexpr int QW = N / 4;
+    for (int idx = tid; idx < N * QW; idx += 256) {
+        const int v = idx / QW, u = idx - v * QW;
+        const int px = x0 + 4 * u, py = y0 + v;
+        if (py >= D.h || px >= D.w) continue;
+        const uint32_t* r = S + (HL + v) * (PB / 4) + (HL + 4 * u) / 4;
+        const uint32_t out = (HL & 3) ? __funnelshift_r(r[0], r[1], 8 * (HL & 3)) : r[0];
+        const int nv = min(4, D.w - px);
+        const bool colwork = px <= P || px + nv - 1 >= D.w - 1 - P;
+        auto put_row = [&](int t) {
+            uint8_t* drow = lv + (long long)t * D.pitch;
+            if (nv == 4) *reinterpret_cast<uint32_t*>(drow + px) = out;
+            else
+                for (int i = 0; i < nv; ++i) drow[px + i] = (uint8_t)(out >> (8 * i));
+            if (colwork) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int x = px + i;
+                    const uint8_t b = (uint8_t)(out >> (8 * i));
+                    if (i < nv && x >= 1 && x <= P) drow[-x] = b;
+                    if (i < nv && x >= D.w - 1 - P && x <= D.w - 2) drow[2 * (D.w - 1) - x] = b;
+                }
+            }
+        };
+        put_row(py);
+        if (py >= 1 && py <= P) put_row(-py);
+        if (py >= D.h - 1 - P && py <= D.h - 2) put_row(2 * (D.h - 1) - py);
+    }
+}
+
+// level l (region in S, pitch PBS bytes) -> level l+1 region (RWN x RWN outputs, pitch PBD bytes): slot (i, j) of the next
+// level takes rows 2i .. 2i+4 and columns 2j .. 2j+4 of this one
+template <int RWN, int PBS, int PBD>
+__device__ __forceinline__ void fused_down(const uint32_t* __restrict__ S, uint32_t* __restrict__ Dn, int tid)
+{
+    constexpr int Q = (RWN + 3) / 4;
+    for (int idx = tid; idx < RWN * Q; idx += 256) {
+        const int i = idx / Q, q = idx - i * Q;
+        uint32_t acc0 = 128, acc1 = 128, acc2 = 128, acc3 = 128;
+        const uint32_t* r0 = S + (2 * i) * (PBS / 4) + 2 * q;
+#pragma unroll
+        for (int j = 0; j < 5; ++j) {
+            const uint32_t k = j == 0 || j == 4 ? 1 : j == 2 ? 6 : 4;
+            const uint32_t* r = r0 + j * (PBS / 4);
+            const uint32_t w0 = r[0], w1 = r[1], w2 = r[2];
+            const uint32_t Cw = k | ((4 * k) << 8) | ((6 * k) << 16) | ((4 * k) << 24);   // (1, 4, 6, 4) k
+            const uint32_t E = k;                                                      // (1, 0, 0, 0) k
+            const uint32_t A = (k << 16) | ((4 * k) << 24);                            // (0, 0, 1, 4) k
+            const uint32_t B = (6 * k) | ((4 * k) << 8) | (k << 16);                   // (6, 4, 1, 0) k
+            acc0 = __dp4a(w0, Cw, acc0); acc0 = __dp4a(w1, E, acc0);
+            acc1 = __dp4a(w0, A, acc1); acc1 = __dp4a(w1, B, acc1);
+            acc2 = __dp4a(w1, Cw, acc2); acc2 = __dp4a(w2, E, acc2);
+            acc3 = __dp4a(w1, A, acc3); acc3 = __dp4a(w2, B, acc3);
+        }
+        Dn[i * (PBD / 4) + q] = pack4(acc0 >> 8, acc1 >> 8, acc2 >> 8, acc3 >> 8);
+    }
+}
+
+// slots of a region (origin (lox, loy), RW x RW, pitch PB) that lie outside the level take the value of the inside pixel
+// BORDER_REFLECT_101 maps them to
+template <int RW, int PB>
+__device__ __forceinline__ void fused_reflect(uint32_t* __restrict__ S, const LevelGeom L, int lox, int loy, int tid)
+{
+    if (lox >= 0 && loy >= 0 && lox + RW <= L.w && loy + RW <= L.h) return;   // CTA-uniform: nothing outside
+    uint8_t* B = reinterpret_cast<uint8_t*>(S);
+    for (int idx = tid; idx < RW * RW; idx += 256) {
+        const int i = idx / RW, j = idx - i * RW;
+        const int y = loy + i, x = lox + j;
+        if (x >= 0 && x < L.w && y >= 0 && y < L.h) continue;
+        const int ri = min(max(reflect101(y, L.h) - loy, 0), RW - 1), rj = min(max(reflect101(x, L.w) - lox, 0), RW - 1);
+        B[i * PB + j] = B[ri * PB + rj];
+    }
+}
+
+template <int NL>
+__global__ void __launch_bounds__(256) pyramid_fused_kernel(const FusedPyrArgs a)
+{
+    using G = FusedGeo<NL>;
+    __shared__ __align__(16) uint32_t smem[G::total_words];
+    const int tid = threadIdx.x;
+    const int lane = blockIdx.z;
+    const uint8_t* src = a.raw + (size_t)lane * a.raw_lane;
+    uint8_t* base = a.pyr + (size_t)lane * a.lane_bytes;
+    const int P = a.P;
+
+    // ---- level-0 region, BORDER_REFLECT_101 applied while loading; interior words: two aligned loads + funnel shift
+    {
+        const LevelGeom L = a.lv[0];
+        constexpr int PW = G::pb(0) / 4;
+        const int lox = blockIdx.x * kFT - G::hl(0), loy = blockIdx.y * kFT - G::hl(0);
+        for (int idx = tid; idx < G::rw(0) * PW; idx += 256) {
+            const int r = idx / PW, cw = idx - r * PW;
+            const int gx = lox + 4 * cw;
+            const uint8_t* row = src + (size_t)reflect101(loy + r, L.h) * a.raw_pitch;
+            uint32_t v;
+            if (gx >= 0 && gx + 7 < L.w) {
+                const uintptr_t addr = reinterpret_cast<uintptr_t>(row + gx);
+                const uint32_t* wp = reinterpret_cast<const uint32_t*>(addr & ~(uintptr_t)3);
+                v = __funnelshift_r(__ldg(wp), __ldg(wp + 1), 8 * (int)(addr & 3));
+            } else {
+                v = 0;
+#pragma unroll
+                for (int b = 0; b < 4; ++b) v |= (uint32_t)__ldg(row + reflect101(gx + b, L.w)) << (8 * b);
+            }
+            smem[idx] = v;
+        }
+    }
+    __syncthreads();
+    fused_emit<G::n(0), G::hl(0), G::pb(0)>(smem, base + a.lv[0].off, a.lv[0], P, blockIdx.x * kFT, blockIdx.y * kFT, tid);
+    if constexpr (NL >= 2) {
+        fused_down<G::rw(1), G::pb(0), G::pb(1)>(smem + G::off(0), smem + G::off(1), tid);
+        __syncthreads();
+        fused_reflect<G::rw(1), G::pb(1)>(smem + G::off(1), a.lv[1], blockIdx.x * G::n(1) - G::hl(1), blockIdx.y * G::n(1) - G::hl(1), tid);
+        __syncthreads();
+        fused_emit<G::n(1), G::hl(1), G::pb(1)>(smem + G::off(1), base + a.lv[1].off, a.lv[1], P, blockIdx.x * G::n(1), blockIdx.y * G::n(1), tid);
+    }
+    if constexpr (NL >= 3) {
+        fused_down<G::rw(2), G::pb(1), G::pb(2)>(smem + G::off(1), smem + G::off(2), tid);
+        __syncthreads();
+        fused_reflect<G::rw(2), G::pb(2)>(smem + G::off(2), a.lv[2], blockIdx.x * G::n(2) - G::hl(2), blockIdx.y * G::n(2) - G::hl(2), tid);
+        __syncthreads();
+        fused_emit<G::n(2), G::hl(2), G::pb(2)>(smem + G::off(2), base + a.lv[2].off, a.lv[2], P, blockIdx.x * G::n(2), blockIdx.y * G::n(2), tid);
+    }
+    if constexpr (NL >= 4) {
+        fused_down<G::rw(3), G::pb(2), G::pb(3)>(smem + G::off(2), smem + G::off(3), tid);
+        __syncthreads();
+        fused_emit<G::n(3), G::hl(3), G::pb(3)>(smem + G::off(3), base + a.lv[3].off, a.lv[3], P, blockIdx.x * G::n(3), blockIdx.y * G::n(3), tid);
+    }
+}
+
 void launch_ingest(cudaStream_t st, const uint8_t* raw, size_t raw_pitch, size_t raw_lane, uint8_t* pyr,
                    const PyrGeom& g, int batch, long long* launches)
 {
@@ -239,6 +413,26 @@ void launch_bgr2gray(cudaStream_t st, const uint8_t* src, size_t src_pitch, size
     dim3 grid(((w + 3) / 4 + 127) / 128, h, batch);
     bgr2gray_kernel<<<grid, 128, 0, st>>>(src, src_pitch, src_lane, dst, dst_pitch, dst_lane, w);
     if (launches) ++*launches;
+}
+
+int launch_pyramid_fused(cudaStream_t st, const uint8_t* raw, size_t raw_pitch, size_t raw_lane, uint8_t* pyr,
+                         const PyrGeom& g, int batch, long long* launches)
+{
+    const int nl = std::min(g.nlevels, 4);
+    for (int l = 0; l < nl; ++l)   // the margin must be narrower than every fused level (one mirror image per side)
+        if (g.P > g.lv[l].w - 1 || g.P > g.lv[l].h - 1) return 0;
+    FusedPyrArgs a{};
+    a.raw = raw; a.raw_pitch = raw_pitch; a.raw_lane = raw_lane; a.pyr = pyr; a.lane_bytes = g.lane_bytes; a.P = g.P;
+    for (int l = 0; l < nl; ++l) a.lv[l] = g.lv[l];
+    dim3 grid((g.lv[0].w + kFT - 1) / kFT, (g.lv[0].h + kFT - 1) / kFT, batch);
+    switch (nl) {
+    case 1: pyramid_fused_kernel<1><<<grid, 256, 0, st>>>(a); break;
+    case 2: pyramid_fused_kernel<2><<<grid, 256, 0, st>>>(a); break;
+    case 3: pyramid_fused_kernel<3><<<grid, 256, 0, st>>>(a); break;
+    default: pyramid_fused_kernel<4><<<grid, 256, 0, st>>>(a); break;
+    }
+    if (launches) ++*launches;
+    return nl;
 }
 
 void launch_pyrdown(cudaStream_t st, uint8_t* pyr, const PyrGeom& g, int level, int batch, long long* launches)

@@ -61,6 +61,10 @@ __host__ __device__ inline int reflect101(int i, int n)
 // raw image (pitch raw_pitch, lane stride raw_lane) -> padded level 0 of every lane
 void launch_ingest(cudaStream_t st, const uint8_t* raw, size_t raw_pitch, size_t raw_lane, uint8_t* pyr,
                    const PyrGeom& g, int batch, long long* launches);
+// raw image -> padded levels 0 .. min(nlevels, 4) - 1 of every lane in one launch; returns the number of levels it built
+// (0: geometry not covered -- a margin wider than a level -- use launch_ingest + launch_pyrdown)
+int launch_pyramid_fused(cudaStream_t st, const uint8_t* raw, size_t raw_pitch, size_t raw_lane, uint8_t* pyr,
+                         const PyrGeom& g, int batch, long long* launches);
 // interleaved BGR (CV_8UC3) -> gray rows of pitch dst_pitch (a multiple of 4, >= w rounded up to 4), every lane
 void launch_bgr2gray(cudaStream_t st, const uint8_t* src, size_t src_pitch, size_t src_lane, uint8_t* dst, size_t dst_pitch,
                      size_t dst_lane, int w, int h, int batch, long long* launches);
@@ -141,10 +145,9 @@ struct KltArgs {
     unsigned long long* iters; // optional global iteration counter
     unsigned* work;            // track hand-out counter of the persistent variant (zeroed by the launcher)
 };
-// part / reserve: see klt.cu:launch_run.  kKltMain and kKltHelper expect klt_zero_work() to have run first (stream-ordered).
-enum KltPart { kKltAll = 0, kKltMain = 1, kKltHelper = 2 };
-void klt_zero_work(cudaStream_t st, const KltArgs& a);
-void launch_klt(cudaStream_t st, const KltArgs& a, int batch, long long* launches, int part = kKltAll, int reserve = 0);
+void launch_klt(cudaStream_t st, const KltArgs& a, int batch, long long* launches);
+// tracks the LK kernel of this window keeps resident at once on the current device (one one-warp CTA per track)
+int klt_resident_tracks(int win_w, int win_h);
 
 // ------------------------------------------------------------------------------------------------ filter.cu
 struct FilterArgs {

@@ -116,6 +116,30 @@ def test_pyramid_bit_exact(ctx, oracle, shape):
             assert np.array_equal(padded, _reflect_pad(ref[l], m)), (shape, win, l)
 
 
+@pytest.mark.parametrize("shape", [(1241, 376), (130, 65), (64, 48), (1920, 1080)])
+def test_pyramid_per_level_launches(oracle, shape, monkeypatch):
+    """SVO_GPU_PYR_FUSED=0: ingest + one pyrDown launch per level (the path tiny levels and levels >= 4 always take) gives the
+    same padded levels as the fused kernel every other test runs, and as the oracle."""
+    w, h = shape
+    img = synth.noise_image(w, h, 10)
+    got = {}
+    for fused in ("1", "0"):
+        monkeypatch.setenv("SVO_GPU_PYR_FUSED", fused)
+        with capi.Context(max_w=w, max_h=h, max_levels=6, max_points=1024, max_batch=1) as c:
+            c.upload(0, img)
+            n0 = c.launch_count
+            levels = c.build_pyramid(0, (21, 21), 5)
+            got[fused] = (levels, c.launch_count - n0, [c.download_level_padded(0, l)[0] for l in range(levels + 1)])
+    ref = oracle.orc_pyramid(img, (21, 21), 5)
+    assert got["1"][0] == got["0"][0] == len(ref) - 1
+    assert got["0"][1] == 2 + got["0"][0]                       # ingest, ingest edge, one launch per further level
+    if min(w, h) > 2 * 33:                                       # margin 32 narrower than levels 0 and 1: the fused kernel ran
+        assert got["1"][1] < got["0"][1]
+    for l, (a, b) in enumerate(zip(got["1"][2], got["0"][2])):
+        assert np.array_equal(a, b), (shape, l)
+        assert np.array_equal(a, _reflect_pad(ref[l], (a.shape[0] - ref[l].shape[0]) // 2)), (shape, l)
+
+
 # ------------------------------------------------------------------------------------------------ bucketing
 def _bucket_cases():
     rng = np.random.default_rng(0)

@@ -47,13 +47,13 @@ def test_step_matches_cpu_pipeline(oracle, mask_half):
         assert ctx.last_klt_iterations > 0
 
 
-def test_step_detection_beside_tracking(oracle, monkeypatch):
-    """SVO_GPU_STEP_OVERLAP=1 (read by svo_gpu_create): mask -> FAST -> bucketing on a second stream beside the LK kernel,
-    whose work queue is then served by a main and a helper launch.  Same answers as the back-to-back step, and the profiled
-    stage times stay meaningful."""
+@pytest.mark.parametrize("overlap", ["1", "0"])
+def test_step_detection_beside_tracking(oracle, monkeypatch, overlap):
+    """SVO_GPU_STEP_OVERLAP (read by svo_gpu_create): 1 = FAST -> bucketing on a second stream beside the LK kernel, 0 = back to
+    back on one stream (unset, as in every other test: decided per call -- these three small lanes overlap).  Same answers,
+    and the profiled stage times stay meaningful."""
     from oracle.cpu_pipeline import CpuFrontend
-    monkeypatch.setenv("SVO_GPU_STEP_OVERLAP", "1")
-    monkeypatch.setenv("SVO_GPU_KLT_RESERVE", "4")
+    monkeypatch.setenv("SVO_GPU_STEP_OVERLAP", overlap)
     seqs = _seqs()
     B = seqs.shape[0]
     with capi.Context(max_w=W, max_h=H, max_levels=4, max_points=8192, max_batch=B) as ctx:
