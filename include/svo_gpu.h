@@ -210,8 +210,17 @@ SVO_GPU_API int svo_gpu_keyframe(svo_gpu_ctx* ctx, int slot_left, int slot_right
 
 /* ---------------------------------------------------------------------------------------------- per-frame step - */
 
-/* Parameters of one front-end frame, i.e. what Tracking::startStereo does per key-frame (src/tracking.cpp:240-257):
- * trackFrames(prev, curr) (:154-179) then extractFeatures(curr) (:74-92) with bucketing at the "todo" of :88. */
+/* Parameters of one front-end frame, i.e. what Tracking::startStereo does per frame (src/tracking.cpp:240-257):
+ * trackFrames(prev, curr) (:154-179) then, on a key-frame, extractFeatures(curr) (:74-92) with bucketing at the "todo" of :88.
+ * Two track policies:
+ *   carry_tracks == 0  every frame is a key-frame and the lane's tracks are RE-SEEDED from the first max_tracks bucketed
+ *                      detections (a fixed, maximal per-frame load: what bench.py times);
+ *   carry_tracks != 0  the reference's loop: the LK survivors (status != 0, input order, src/tracking.cpp:168-175) are the
+ *                      lane's tracks for the next frame; detection runs only on a key-frame -- the lane's first frame, or
+ *                      when the frame before was not a key-frame and ended with fewer than features_to_track tracks
+ *                      (src/tracking.cpp:69-70) -- with the mask around the points LK started from (:77), and the bucketed
+ *                      detections are appended after the survivors (StereoFrame::insertFeatures, :254) up to max_tracks.
+ *                      The decision is taken per lane on the device; lanes that are not key-frames skip FAST and bucketing. */
 typedef struct svo_gpu_step_params {
     int w, h;               /* image size of every lane */
     int fast_threshold;     /* include/config_reader.h:36 (20) */
@@ -227,6 +236,8 @@ typedef struct svo_gpu_step_params {
     int criteria_type;      /* COUNT + EPS */
     int flags;              /* src/tracking.cpp:164 (OPTFLOW_LK_GET_MIN_EIGENVALS) */
     double min_eig_threshold; /* OpenCV default 1e-4 */
+    int carry_tracks;       /* see above */
+    int features_to_track;  /* configs/config.yaml:15 (70); used with carry_tracks */
 } svo_gpu_step_params;
 
 /* Host-side views of one step's results; any pointer may be NULL (that output is then left on the device).
@@ -244,6 +255,12 @@ typedef struct svo_gpu_step_outputs {
     int* n_bucketed;        /* [batch] features kept by bucketing; the first max_tracks of them are the new tracks */
     float* bucket_xy;       /* [batch][bucket_capacity][2] */
     int bucket_capacity;
+    /* carry_tracks mode (zero / NULL otherwise): */
+    int* keyframe;          /* [batch] 1 if detection ran for the lane in this step (StereoFrame::isKeyFrame) */
+    int* n_survived;        /* [batch] LK survivors = the head of the lane's next track list, in input order */
+    int* survivor_index;    /* [batch][track_capacity] position in this step's track list of survivor k (carries
+                               Feature::mapPoint over, src/tracking.cpp:171); the next track list is the survivors'
+                               next_xy followed by the first min(n_bucketed, max_tracks - n_survived) bucket_xy entries */
 } svo_gpu_step_outputs;
 
 /* One frame of `batch` independent streams: ingest images[b] (host or device memory), build its pyramid, run LK from

@@ -80,7 +80,7 @@ class StepParams(C.Structure):
                 ("mask_half", C.c_float), ("bucket_size", C.c_int), ("per_bucket", C.c_int), ("max_tracks", C.c_int),
                 ("win_w", C.c_int), ("win_h", C.c_int), ("max_level", C.c_int), ("max_count", C.c_int),
                 ("epsilon", C.c_double), ("criteria_type", C.c_int), ("flags", C.c_int),
-                ("min_eig_threshold", C.c_double)]
+                ("min_eig_threshold", C.c_double), ("carry_tracks", C.c_int), ("features_to_track", C.c_int)]
 
 
 class KeyframeParams(C.Structure):
@@ -96,7 +96,8 @@ class StepOutputs(C.Structure):
     _fields_ = [("n_tracked", C.c_void_p), ("next_xy", C.c_void_p), ("status", C.c_void_p), ("err", C.c_void_p),
                 ("track_capacity", C.c_int), ("n_keypoints", C.c_void_p), ("kp_xy", C.c_void_p),
                 ("kp_response", C.c_void_p), ("kp_capacity", C.c_int), ("n_bucketed", C.c_void_p),
-                ("bucket_xy", C.c_void_p), ("bucket_capacity", C.c_int)]
+                ("bucket_xy", C.c_void_p), ("bucket_capacity", C.c_int), ("keyframe", C.c_void_p),
+                ("n_survived", C.c_void_p), ("survivor_index", C.c_void_p)]
 
 
 class SvoGpuError(RuntimeError):

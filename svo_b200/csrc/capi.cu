@@ -36,7 +36,7 @@ struct Slot {
 // one submitted step (svo_gpu_step_submit .. svo_gpu_step_wait): its pinned read-back scratch, events and output views
 struct StepTicket {
     bool busy = false;
-    int* hs = nullptr;            // pinned, 4 * max_batch + 16 ints: tracked, keypoints, bucketed, bucket error flags, LK iterations
+    int* hs = nullptr;            // pinned, 6 * max_batch + 16 ints: tracked, keypoints, bucketed, bucket error flags, key-frame flags, survivors, LK iterations
     cudaEvent_t done = nullptr;
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t eva[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -75,7 +75,9 @@ struct svo_gpu_ctx {
     uint8_t* trk_status = nullptr;
     float* trk_err = nullptr;
     int* trk_n = nullptr;         // [B]
-    int* step_summary = nullptr;  // [3][B] keypoints, bucketed, bucket error flags of the step (one read-back)
+    int* step_summary = nullptr;  // [5][B] keypoints, bucketed, bucket error flags, key-frame flags, survivors of the step (one
+                                  // read-back) + [B] arrival counters of next_tracks_kernel (zero between launches)
+    int* lane_kf = nullptr;       // [B] carry_tracks mode: the lane's frame being processed is a key-frame
     int* int_max = nullptr;       // [B] all INT_MAX: "n is given by n_max" for the host-pointer calls
     unsigned long long* d_iters = nullptr;
     long long last_iters = 0;
@@ -86,7 +88,7 @@ struct svo_gpu_ctx {
     float* flt_err = nullptr;
     int* flt_n = nullptr;         // [B]
     // pinned scratch for small read-backs
-    int* h_small = nullptr;       // 4 * max_batch + 16 ints
+    int* h_small = nullptr;       // 6 * max_batch + 16 ints
     int fetch_hint = 0;           // keypoints svo_gpu_fast last returned (+ 25 %): copied back together with the count
     int bucket_fetch_hint = 0;    // same for svo_gpu_bucket
     uint8_t* h_bucket = nullptr;  // pinned staging of svo_gpu_bucket's speculative read-back (bucket_stage_cap entries)
@@ -260,7 +262,8 @@ static int create_buffers(svo_gpu_ctx* ctx)
     if (int r = dmalloc(ctx, ctx->trk_err, B * NP)) return r;
     if (int r = dmalloc(ctx, ctx->trk_n, B)) return r;
     if (int r = dmalloc(ctx, ctx->int_max, B)) return r;
-    if (int r = dmalloc(ctx, ctx->step_summary, 3 * B)) return r;
+    if (int r = dmalloc(ctx, ctx->step_summary, 6 * B)) return r;
+    if (int r = dmalloc(ctx, ctx->lane_kf, B)) return r;
     if (int r = dmalloc(ctx, ctx->d_iters, 2)) return r;   // [0] LK iterations, [1] LK work counter
     if (int r = dmalloc(ctx, ctx->flt_index, B * NP)) return r;
     if (int r = dmalloc(ctx, ctx->flt_a, B * NP)) return r;
@@ -268,16 +271,19 @@ static int create_buffers(svo_gpu_ctx* ctx)
     if (int r = dmalloc(ctx, ctx->flt_err, B * NP)) return r;
     if (int r = dmalloc(ctx, ctx->flt_n, B)) return r;
     CK(cudaMemsetAsync(ctx->trk_n, 0, sizeof(int) * B, ctx->st));
+    CK(cudaMemsetAsync(ctx->flt_n, 0, sizeof(int) * B, ctx->st));
+    CK(cudaMemsetAsync(ctx->step_summary, 0, sizeof(int) * 6 * B, ctx->st));
     CK(cudaMemsetAsync(ctx->d_iters, 0, sizeof(unsigned long long), ctx->st));
     {
         std::vector<int> big(B, INT_MAX);
         CK(cudaMemcpy(ctx->int_max, big.data(), sizeof(int) * B, cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(ctx->lane_kf, big.data(), sizeof(int) * B, cudaMemcpyHostToDevice));   // non-zero: first frames are key-frames
     }
-    CK(cudaMallocHost(reinterpret_cast<void**>(&ctx->h_small), sizeof(int) * (4 * B + 16)));
+    CK(cudaMallocHost(reinterpret_cast<void**>(&ctx->h_small), sizeof(int) * (6 * B + 16)));
     ctx->bucket_stage_cap = (int)std::min<size_t>(NP, 16384);
     CK(cudaMallocHost(reinterpret_cast<void**>(&ctx->h_bucket), (sizeof(float2) + sizeof(int)) * (size_t)ctx->bucket_stage_cap));
     for (auto& tk : ctx->tickets) {
-        CK(cudaMallocHost(reinterpret_cast<void**>(&tk.hs), sizeof(int) * (4 * B + 16)));
+        CK(cudaMallocHost(reinterpret_cast<void**>(&tk.hs), sizeof(int) * (6 * B + 16)));
         CK(cudaEventCreateWithFlags(&tk.done, cudaEventDisableTiming));
         for (auto& e : tk.ev) CK(cudaEventCreate(&e));
         for (auto& e : tk.eva) CK(cudaEventCreate(&e));
@@ -378,7 +384,7 @@ extern "C" int svo_gpu_destroy(svo_gpu_ctx* ctx)
     void* bufs[] = {ctx->fb.rowtotal, ctx->fb.segcnt, ctx->fb.segkp, ctx->fb.kp_xy, ctx->fb.kp_resp, ctx->fb.kp_count,
                     ctx->mask.p, ctx->bgr_stage.p, ctx->bb.out_xy, ctx->bb.out_age, ctx->bb.out_count, ctx->bb.err_flag, ctx->cell_slots.p,
                     ctx->cell_cnt.p, ctx->cell_last.p, ctx->bk_in_xy, ctx->bk_in_age, ctx->trk_xy, ctx->nxt_xy,
-                    ctx->trk_status, ctx->trk_err, ctx->trk_n, ctx->int_max, ctx->step_summary, ctx->d_iters, ctx->flt_index, ctx->flt_a,
+                    ctx->trk_status, ctx->trk_err, ctx->trk_n, ctx->int_max, ctx->step_summary, ctx->lane_kf, ctx->d_iters, ctx->flt_index, ctx->flt_a,
                     ctx->flt_b, ctx->flt_err, ctx->flt_n};
     for (void* p : bufs) cudaFree(p);
     if (ctx->h_small) cudaFreeHost(ctx->h_small);

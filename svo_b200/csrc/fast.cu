@@ -90,6 +90,7 @@ __global__ void __launch_bounds__(NT) fast_tile_kernel(const uint8_t* __restrict
                                                        size_t mask_pitch, size_t mask_lane, FastBufs fb, int ntx,
                                                        FastMaskPts mp)
 {
+    if (mp.lane_active && mp.lane_active[blockIdx.z] == 0) return;   // this lane detects nothing in this call (CTA-uniform)
     __shared__ __align__(16) uint32_t simg_pad[RH * RWW + 2];   // one pad word on each side: ring_word reads words g-1, g+1
     __shared__ __align__(16) uint32_t sbest_pad[SH * RWW + 2];  // excess of the score over the threshold, one byte per pixel,
                                                                 // same column layout as the staged image (0 = no corner)
@@ -323,7 +324,8 @@ void launch_fast(cudaStream_t st, const uint8_t* raw, size_t raw_pitch, size_t r
                  int nms, const uint8_t* mask, size_t mask_pitch, size_t mask_lane, const FastBufs& fb, int batch,
                  long long* launches, int small_ctas, const FastMaskPts* mask_pts)
 {
-    const FastMaskPts mp = mask_pts && mask_pts->pts && mask_pts->n_max > 0 ? *mask_pts : FastMaskPts{};
+    FastMaskPts mp = mask_pts ? *mask_pts : FastMaskPts{};
+    if (!mp.pts || mp.n_max <= 0) { mp.pts = nullptr; mp.n_max = 0; }
     threshold = threshold < 0 ? 0 : (threshold > 255 ? 255 : threshold);
     cudaMemsetAsync(fb.rowtotal, 0, sizeof(int) * (size_t)fb.rows_cap * batch, st);
     if (w < 7 || h < 7) {   // no candidate pixel at all (OpenCV returns an empty list)

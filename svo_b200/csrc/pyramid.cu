@@ -277,18 +277,71 @@ __device__ __forceinline__ void fused_down(const uint32_t* __restrict__ S, uint3
 }
 
 // slots of a region (origin (lox, loy), RW x RW, pitch PB) that lie outside the level take the value of the inside pixel
-// BORDER_REFLECT_101 maps them to
+// BORDER_REFLECT_101 maps them to: first the outside columns of every row, then (after a barrier) the outside rows as copies
+// of whole rows, which brings the corners along.  Only CTAs at the level's border have any (CTA-uniform test).
 template <int RW, int PB>
 __device__ __forceinline__ void fused_reflect(uint32_t* __restrict__ S, const LevelGeom L, int lox, int loy, int tid)
 {
-    if (lox >= 0 && loy >= 0 && lox + RW <= L.w && loy + RW <= L.h) return;   // CTA-uniform: nothing outside
+    const int nl = max(-lox, 0), nr = max(lox + RW - L.w, 0);      // outside columns on the left / right
+    const int nt = max(-loy, 0), nb = max(loy + RW - L.h, 0);      // outside rows above / below
+    if ((nl | nr | nt | nb) == 0) return;
     uint8_t* B = reinterpret_cast<uint8_t*>(S);
-    for (int idx = tid; idx < RW * RW; idx += 256) {
-        const int i = idx / RW, j = idx - i * RW;
-        const int y = loy + i, x = lox + j;
-        if (x >= 0 && x < L.w && y >= 0 && y < L.h) continue;
-        const int ri = min(max(reflect101(y, L.h) - loy, 0), RW - 1), rj = min(max(reflect101(x, L.w) - lox, 0), RW - 1);
-        B[i * PB + j] = B[ri * PB + rj];
+    const int tx = tid & 15, ty = tid >> 4;
+    if (nl | nr) {
+        for (int i = ty; i < RW; i += 16)
+            for (int c = tx; c < nl + nr; c += 16) {
+                const int j = c < nl ? c : RW - nr + (c - nl);
+                const int rj = min(max(reflect101(lox + j, L.w) - lox, 0), RW - 1);
+                B[i * PB + j] = B[i * PB + rj];
+            }
+        __syncthreads();
+    }
+    if (nt | nb) {
+        for (int r = ty; r < nt + nb; r += 16) {
+            const int i = r < nt ? r : RW - nb + (r - nt);
+            const int ri = min(max(reflect101(loy + i, L.h) - loy, 0), RW - 1);
+            for (int j = tx; j < RW; j += 16) B[i * PB + j] = B[ri * PB + j];
+        }
+    }
+}
+
+// owned tile (N x N, N a multiple of 16) -> the padded level, 16 bytes per thread and row: one aligned 128-bit store for
+// the interior (tile origins and level rows are 16 B-aligned), bytes only at a ragged right edge and for the mirror columns
+template <int N, int HL, int PB>
+__device__ __forceinline__ void fused_emit16(const uint32_t* __restrict__ S, uint8_t* __restrict__ lv, const LevelGeom D, int P,
+                                             int x0, int y0, int tid)
+{
+    constexpr int CW = N / 16;
+    for (int idx = tid; idx < N * CW; idx += 256) {
+        const int v = idx / CW, c = idx - v * CW;
+        const int px = x0 + 16 * c, py = y0 + v;
+        if (py >= D.h || px >= D.w) continue;
+        const uint32_t* r = S + (HL + v) * (PB / 4) + HL / 4 + 4 * c;
+        uint32_t o[4];
+        if (HL & 3) {
+            const uint32_t w0 = r[0], w1 = r[1], w2 = r[2], w3 = r[3], w4 = r[4];
+            o[0] = __funnelshift_r(w0, w1, 8 * (HL & 3)); o[1] = __funnelshift_r(w1, w2, 8 * (HL & 3));
+            o[2] = __funnelshift_r(w2, w3, 8 * (HL & 3)); o[3] = __funnelshift_r(w3, w4, 8 * (HL & 3));
+        } else { o[0] = r[0]; o[1] = r[1]; o[2] = r[2]; o[3] = r[3]; }
+        const int nv = min(16, D.w - px);
+        const bool colwork = px <= P || px + nv - 1 >= D.w - 1 - P;
+        auto put_row = [&](int t) {
+            uint8_t* drow = lv + (long long)t * D.pitch;
+            if (nv == 16) *reinterpret_cast<uint4*>(drow + px) = make_uint4(o[0], o[1], o[2], o[3]);
+            else
+                for (int i = 0; i < nv; ++i) drow[px + i] = (uint8_t)(o[i >> 2] >> (8 * (i & 3)));
+            if (colwork) {
+                for (int i = 0; i < nv; ++i) {
+                    const int x = px + i;
+                    const uint8_t b = (uint8_t)(o[i >> 2] >> (8 * (i & 3)));
+                    if (x >= 1 && x <= P) drow[-x] = b;
+                    if (x >= D.w - 1 - P && x <= D.w - 2) drow[2 * (D.w - 1) - x] = b;
+                }
+            }
+        };
+        put_row(py);
+        if (py >= 1 && py <= P) put_row(-py);
+        if (py >= D.h - 1 - P && py <= D.h - 2) put_row(2 * (D.h - 1) - py);
     }
 }
 
@@ -303,36 +356,50 @@ __global__ void __launch_bounds__(256) pyramid_fused_kernel(const FusedPyrArgs a
     uint8_t* base = a.pyr + (size_t)lane * a.lane_bytes;
     const int P = a.P;
 
-    // ---- level-0 region, BORDER_REFLECT_101 applied while loading; interior words: two aligned loads + funnel shift
+    // ---- level-0 region, BORDER_REFLECT_101 applied while loading.  A warp takes a region row at a time (lanes = words);
+    //      CTAs whose region lies inside the frame (CTA-uniform) load two aligned words + a funnel shift per word, nothing else
     {
         const LevelGeom L = a.lv[0];
         constexpr int PW = G::pb(0) / 4;
+        static_assert(PW <= 32, "a region row is one warp pass");
         const int lox = blockIdx.x * kFT - G::hl(0), loy = blockIdx.y * kFT - G::hl(0);
-        for (int idx = tid; idx < G::rw(0) * PW; idx += 256) {
-            const int r = idx / PW, cw = idx - r * PW;
-            const int gx = lox + 4 * cw;
-            const uint8_t* row = src + (size_t)reflect101(loy + r, L.h) * a.raw_pitch;
-            uint32_t v;
-            if (gx >= 0 && gx + 7 < L.w) {
-                const uintptr_t addr = reinterpret_cast<uintptr_t>(row + gx);
-                const uint32_t* wp = reinterpret_cast<const uint32_t*>(addr & ~(uintptr_t)3);
-                v = __funnelshift_r(__ldg(wp), __ldg(wp + 1), 8 * (int)(addr & 3));
+        const int warp = tid >> 5, ln = tid & 31;
+        const bool inside = lox >= 0 && loy >= 0 && lox + 4 * PW + 4 <= L.w && loy + G::rw(0) <= L.h;
+        if (ln < PW) {
+            if (inside) {
+                const uint8_t* p = src + (size_t)(loy + warp) * a.raw_pitch + lox + 4 * ln;
+                for (int r = warp; r < G::rw(0); r += 8, p += 8 * a.raw_pitch) {
+                    const uintptr_t addr = reinterpret_cast<uintptr_t>(p);
+                    const uint32_t* wp = reinterpret_cast<const uint32_t*>(addr & ~(uintptr_t)3);
+                    smem[r * PW + ln] = __funnelshift_r(__ldg(wp), __ldg(wp + 1), 8 * (int)(addr & 3));
+                }
             } else {
-                v = 0;
+                const int gx = lox + 4 * ln;
+                for (int r = warp; r < G::rw(0); r += 8) {
+                    const uint8_t* row = src + (size_t)reflect101(loy + r, L.h) * a.raw_pitch;
+                    uint32_t v;
+                    if (gx >= 0 && gx + 7 < L.w) {
+                        const uintptr_t addr = reinterpret_cast<uintptr_t>(row + gx);
+                        const uint32_t* wp = reinterpret_cast<const uint32_t*>(addr & ~(uintptr_t)3);
+                        v = __funnelshift_r(__ldg(wp), __ldg(wp + 1), 8 * (int)(addr & 3));
+                    } else {
+                        v = 0;
 #pragma unroll
-                for (int b = 0; b < 4; ++b) v |= (uint32_t)__ldg(row + reflect101(gx + b, L.w)) << (8 * b);
+                        for (int b = 0; b < 4; ++b) v |= (uint32_t)__ldg(row + reflect101(gx + b, L.w)) << (8 * b);
+                    }
+                    smem[r * PW + ln] = v;
+                }
             }
-            smem[idx] = v;
         }
     }
     __syncthreads();
-    fused_emit<G::n(0), G::hl(0), G::pb(0)>(smem, base + a.lv[0].off, a.lv[0], P, blockIdx.x * kFT, blockIdx.y * kFT, tid);
+    fused_emit16<G::n(0), G::hl(0), G::pb(0)>(smem, base + a.lv[0].off, a.lv[0], P, blockIdx.x * kFT, blockIdx.y * kFT, tid);
     if constexpr (NL >= 2) {
         fused_down<G::rw(1), G::pb(0), G::pb(1)>(smem + G::off(0), smem + G::off(1), tid);
         __syncthreads();
         fused_reflect<G::rw(1), G::pb(1)>(smem + G::off(1), a.lv[1], blockIdx.x * G::n(1) - G::hl(1), blockIdx.y * G::n(1) - G::hl(1), tid);
         __syncthreads();
-        fused_emit<G::n(1), G::hl(1), G::pb(1)>(smem + G::off(1), base + a.lv[1].off, a.lv[1], P, blockIdx.x * G::n(1), blockIdx.y * G::n(1), tid);
+        fused_emit16<G::n(1), G::hl(1), G::pb(1)>(smem + G::off(1), base + a.lv[1].off, a.lv[1], P, blockIdx.x * G::n(1), blockIdx.y * G::n(1), tid);
     }
     if constexpr (NL >= 3) {
         fused_down<G::rw(2), G::pb(1), G::pb(2)>(smem + G::off(1), smem + G::off(2), tid);

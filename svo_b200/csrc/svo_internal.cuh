@@ -96,6 +96,7 @@ struct FastMaskPts {
     const int* n_dev = nullptr;
     int n_max = 0;
     float half = 0.f;
+    const int* lane_active = nullptr;   // [B] or nullptr: lanes whose flag is 0 are skipped altogether (they report 0 keypoints)
 };
 
 // mask: device u8 plane per lane (pitch mask_pitch, lane stride mask_lane) or nullptr; mask_pts: see above (either, or none)

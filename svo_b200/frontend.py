@@ -11,7 +11,7 @@ from . import capi
 
 REFERENCE_PARAMS = dict(fast_threshold=20, fast_nms=1, mask_half=10.0, bucket_size=32, per_bucket=5, max_tracks=2000,
                         win_w=21, win_h=21, max_level=3, max_count=50, epsilon=0.001, criteria_type=3,
-                        flags=capi.LK_GET_MIN_EIGENVALS, min_eig_threshold=1e-4)
+                        flags=capi.LK_GET_MIN_EIGENVALS, min_eig_threshold=1e-4, carry_tracks=0, features_to_track=70)
 
 
 def make_params(w, h, **over):
@@ -53,6 +53,9 @@ class _Outputs:
         self.n_tracked = buf((batch,), np.int32)
         self.n_keypoints = buf((batch,), np.int32)
         self.n_bucketed = buf((batch,), np.int32)
+        self.keyframe = buf((batch,), np.int32)
+        self.n_survived = buf((batch,), np.int32)
+        self.survivor_index = buf((batch, max(tc, 1)), np.int32)
         self.next_xy = buf((batch, max(tc, 1), 2), np.float32)
         self.status = buf((batch, max(tc, 1)), np.uint8)
         self.err = buf((batch, max(tc, 1)), np.float32)
@@ -64,6 +67,8 @@ class _Outputs:
         o.track_capacity = tc
         o.bucket_xy = self.bucket_xy.ctypes.data
         o.bucket_capacity = bucket_capacity
+        o.keyframe, o.n_survived, o.survivor_index = (self.keyframe.ctypes.data, self.n_survived.ctypes.data,
+                                                      self.survivor_index.ctypes.data)
         self.kp_xy = self.kp_response = None
         if kp_capacity > 0:
             self.kp_xy = buf((batch, kp_capacity, 2), np.float32)
@@ -83,13 +88,14 @@ class Frontend:
         self._pending = []
         self._nsub = 0
         self._bind(self._sets[0])
-        self.d2h_bytes = int(3 * 4 * batch + batch * tc * (8 + 1 + 4) + batch * bucket_capacity * 8 +
-                             batch * kp_capacity * 12)
+        self.d2h_bytes = int(5 * 4 * batch + batch * tc * (8 + 1 + 4) + batch * bucket_capacity * 8 +
+                             batch * kp_capacity * 12 + (batch * tc * 4 if self.pdict["carry_tracks"] else 0))
 
     def _bind(self, s):
         """The public result attributes show set `s` (the step that completed last)."""
         self.out = s.out
-        for name in ("n_tracked", "n_keypoints", "n_bucketed", "next_xy", "status", "err", "bucket_xy", "kp_xy", "kp_response"):
+        for name in ("n_tracked", "n_keypoints", "n_bucketed", "next_xy", "status", "err", "bucket_xy", "kp_xy", "kp_response",
+                     "keyframe", "n_survived", "survivor_index"):
             setattr(self, name, getattr(s, name))
 
     # ---- asynchronous form: submit(t + 1) may precede wait(t); results of a step are visible after ITS wait

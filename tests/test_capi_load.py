@@ -34,9 +34,9 @@ def test_abi_version(lib):
 
 def test_struct_layouts_match_header():
     # svo_gpu_step_params: 12 ints/floats + 2 doubles with natural alignment
-    assert C.sizeof(capi.StepParams) == 72
+    assert C.sizeof(capi.StepParams) == 80
     assert capi.StepParams.epsilon.offset == 48 and capi.StepParams.min_eig_threshold.offset == 64
-    assert C.sizeof(capi.StepOutputs) == 96
+    assert C.sizeof(capi.StepOutputs) == 120 and capi.StepParams.carry_tracks.offset == 72
     # svo_gpu_keyframe_params: 9 ints/floats, pad, double, 2 ints, double, float, pad
     assert C.sizeof(capi.KeyframeParams) == 72
     assert capi.KeyframeParams.epsilon.offset == 40 and capi.KeyframeParams.min_eig_threshold.offset == 56
