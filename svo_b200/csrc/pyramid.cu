@@ -361,19 +361,30 @@ __global__ void __launch_bounds__(256) pyramid_fused_kernel(const FusedPyrArgs a
     {
         const LevelGeom L = a.lv[0];
         constexpr int PW = G::pb(0) / 4;
-        static_assert(PW <= 32, "a region row is one warp pass");
+        static_assert(PW < 32, "a region row (+ one word) is one warp pass");
         const int lox = blockIdx.x * kFT - G::hl(0), loy = blockIdx.y * kFT - G::hl(0);
         const int warp = tid >> 5, ln = tid & 31;
         const bool inside = lox >= 0 && loy >= 0 && lox + 4 * PW + 4 <= L.w && loy + G::rw(0) <= L.h;
-        if (ln < PW) {
+        {
             if (inside) {
-                const uint8_t* p = src + (size_t)(loy + warp) * a.raw_pitch + lox + 4 * ln;
-                for (int r = warp; r < G::rw(0); r += 8, p += 8 * a.raw_pitch) {
-                    const uintptr_t addr = reinterpret_cast<uintptr_t>(p);
-                    const uint32_t* wp = reinterpret_cast<const uint32_t*>(addr & ~(uintptr_t)3);
-                    smem[r * PW + ln] = __funnelshift_r(__ldg(wp), __ldg(wp + 1), 8 * (int)(addr & 3));
+                // one aligned word per lane (lanes 0 .. PW: the row's PW words + the one the last funnel shift needs), all
+                // rows of this warp in flight before the first use; the neighbour's word comes by shuffle
+                constexpr int RMAX = (G::rw(0) + 7) / 8;
+                uint32_t v[RMAX];
+#pragma unroll
+                for (int k = 0; k < RMAX; ++k) {
+                    const int r = min(warp + 8 * k, G::rw(0) - 1);
+                    const uintptr_t addr = reinterpret_cast<uintptr_t>(src + (size_t)(loy + r) * a.raw_pitch + lox);
+                    v[k] = ln <= PW ? __ldg(reinterpret_cast<const uint32_t*>(addr & ~(uintptr_t)3) + ln) : 0u;
                 }
-            } else {
+#pragma unroll
+                for (int k = 0; k < RMAX; ++k) {
+                    const int r = warp + 8 * k;
+                    const int sh = 8 * (int)(reinterpret_cast<uintptr_t>(src + (size_t)(loy + min(r, G::rw(0) - 1)) * a.raw_pitch + lox) & 3);
+                    const uint32_t nxt = __shfl_down_sync(0xffffffffu, v[k], 1);
+                    if (r < G::rw(0) && ln < PW) smem[r * PW + ln] = __funnelshift_r(v[k], nxt, sh);
+                }
+            } else if (ln < PW) {
                 const int gx = lox + 4 * ln;
                 for (int r = warp; r < G::rw(0); r += 8) {
                     const uint8_t* row = src + (size_t)reflect101(loy + r, L.h) * a.raw_pitch;
