@@ -548,6 +548,46 @@ def run_b200(args):
                      "host_binding": binding}
     if h2d:
         line["h2d_probe"] = h2d
+    if not args.no_extras and world == 1:
+        # the reference's own track policy (svo_gpu_step_params.carry_tracks): LK survivors carry over, detection only on
+        # key-frames (src/tracking.cpp:69-70, :168-177, :247-254); same streams, device-resident frames, 2 steps outstanding
+        line["reference_loop"] = {"note": "carry_tracks mode, %d streams, frames resident in HBM; key-frame = the lane's first frame "
+                                          "or a non-key-frame that ended below features_to_track; every step's results are waited for" % S}
+        for ftt in (70, wl["n_tracks"]):
+            try:
+                fe2 = Frontend(ctx, w, h, S, bucket_capacity=cells, carry_tracks=1, features_to_track=ftt, **step_params(wl))
+                n2, kf_sum, trk_sum2 = max(60, K // 3), 0, 0
+
+                def sub2(i):
+                    fe2.submit(dev[i % RING].data_ptr(), None, capi.MEM_DEVICE, pitch, h * pitch)
+
+                def drain(i0, i1, count):
+                    nonlocal kf_sum, trk_sum2
+                    for i in range(i0, i1):
+                        sub2(i)
+                        if fe2.outstanding == 2:
+                            fe2.wait()
+                            if count:
+                                kf_sum += int(fe2.keyframe.sum()); trk_sum2 += int(fe2.n_tracked.sum())
+                    while fe2.outstanding:
+                        fe2.wait()
+                        if count:
+                            kf_sum += int(fe2.keyframe.sum()); trk_sum2 += int(fe2.n_tracked.sum())
+
+                fe2.reset()
+                drain(0, 10, False)
+                torch.cuda.synchronize()
+                ev[4].record(stream)
+                drain(10, 10 + n2, True)
+                ev[5].record(stream)
+                torch.cuda.synchronize()
+                ms2 = ev[4].elapsed_time(ev[5]) / n2
+                line["reference_loop"]["features_to_track_%d" % ftt] = {
+                    "frames_per_s": S / (ms2 * 1e-3), "ms_per_step": ms2, "keyframe_fraction": kf_sum / (S * n2),
+                    "tracks_per_frame": trk_sum2 / (S * n2), "steps": n2}
+            except Exception as e:
+                line["reference_loop"]["features_to_track_%d" % ftt] = {"error": repr(e)[:200]}
+        fe.reset()
     if not args.no_extras:
         try:
             line["single_stream"] = run_single_stream(capi, Frontend, torch, local, wl, np.ascontiguousarray(frames[:, :1]), 200)

@@ -116,7 +116,7 @@ struct svo_gpu_ctx {
     cudaStream_t pyr_st = nullptr;
     cudaEvent_t ev_pyr = nullptr;
     int pyr_async = 1;      // SVO_GPU_STEP_PYR_ASYNC (0 = pyramid on the main stream)
-    int pyr_fused = 1;      // SVO_GPU_PYR_FUSED (0 = ingest + one pyrDown launch per level)
+    int pyr_fused = -1;     // SVO_GPU_PYR_FUSED: -1 = per call (fused for small frame sets), 0 = ingest + one pyrDown launch per level, 1 = fused
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     int overlap = -1;       // SVO_GPU_STEP_OVERLAP: -1 = per call (detection beside LK when LK does not fill the device), 0 / 1 = never / always
     int fast_small = 1;     // SVO_GPU_FAST_SMALL: 128-thread FAST CTAs in the step (0 = 256)
@@ -550,7 +550,16 @@ static int enqueue_pyramid(svo_gpu_ctx* ctx, Slot& s, int win_w, int win_h, int 
     make_geometry(s.g, s.w, s.h, eff + 1, margin_for(win_w, win_h));
     if (int r = ensure(ctx, s.pyr, (size_t)s.g.lane_bytes * (size_t)ctx->max_batch)) return r;
     uint8_t* pyr = static_cast<uint8_t*>(s.pyr.p);
-    int built = ctx->pyr_fused ? launch_pyramid_fused(ps, s.raw, s.raw_pitch, s.raw_lane, pyr, s.g, s.batch, &ctx->launches) : 0;
+    // One fused launch for levels 0..3 when the frame set is small (its CTAs fit the device about twice over: what counts
+    // there is the chain of dependent launches), the streaming per-level kernels when many lanes fill the device anyway
+    // (measured at 64 lanes: 0.069 ms against 0.117 ms for the fused kernel, whose CTAs spend their time between barriers).
+    bool fused = ctx->pyr_fused > 0;
+    if (ctx->pyr_fused < 0) {
+        int sms = 0;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
+        fused = (long long)((s.w + 63) / 64) * ((s.h + 63) / 64) * s.batch <= 10LL * sms;
+    }
+    int built = fused ? launch_pyramid_fused(ps, s.raw, s.raw_pitch, s.raw_lane, pyr, s.g, s.batch, &ctx->launches) : 0;
     if (built == 0) {
         launch_ingest(ps, s.raw, s.raw_pitch, s.raw_lane, pyr, s.g, s.batch, &ctx->launches);
         built = 1;

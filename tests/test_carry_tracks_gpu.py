@@ -15,10 +15,10 @@ pytestmark = pytest.mark.gpu
 W, H = 320, 240
 
 
-def _run(oracle, features_to_track, T, max_tracks, depth, seeds=(5, 6, 7)):
+def _run(oracle, features_to_track, T, max_tracks, depth, seeds=(5, 6, 7), speed=(1.0, 1.0, 1.0)):
     import torch
     from oracle.cpu_pipeline import CpuFrontend
-    seqs = np.stack([synth.sequence(W, H, s, T) for s in seeds])               # [lane, t, h, w]
+    seqs = np.stack([synth.sequence(W, H, s, T, times=[v * t for t in range(T)]) for s, v in zip(seeds, speed)])   # [lane, t, h, w]
     B = len(seeds)
     frames = torch.from_numpy(np.ascontiguousarray(seqs.transpose(1, 0, 2, 3))).pin_memory()
     kfs = []
@@ -67,8 +67,10 @@ def test_reference_loop_with_the_shipped_threshold(oracle, depth):
 
 
 def test_key_frames_fire_per_lane(oracle):
-    """A threshold just under the track count: lanes lose tracks at different rates (image border, low texture), so key-frames
-    fire in some lanes and not in others within the same launch; a key-frame is never followed directly by another."""
-    kf = _run(oracle, 398, 10, 400, 2)
+    """A threshold at the track count and lanes that move at different speeds (6, 0.2 and 3 px per frame): the fast lanes
+    lose tracks at the image border and re-detect, the slow one does not, so key-frames fire in some lanes and not in others
+    within the same launch; a key-frame is never followed directly by another (src/tracking.cpp:69)."""
+    kf = _run(oracle, 400, 10, 400, 2, speed=(3.0, 0.1, 1.5))
     assert kf[0].all() and kf[1:].any() and not kf[1:].all()
+    assert (kf[1:].min(axis=1) != kf[1:].max(axis=1)).any()          # lanes disagree within one step
     assert not (kf[1:] & kf[:-1]).any()
