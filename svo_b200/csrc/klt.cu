@@ -196,10 +196,9 @@ __device__ __forceinline__ void stage_shifted(uint32_t dst0, const uint8_t* __re
     constexpr int OW = RP / 4, RPP = 32 / OW, PASSES = (ROWS + RPP - 1) / RPP;
     const int sh = 8 * (x0 & 3);
     uint32_t lo[PASSES], hi[PASSES];
-    const long long step = (long long)RPP * pitch;
-    const uint8_t* p = src0;
 #pragma unroll
-    for (int k = 0; k < PASSES; ++k, p += step) {
+    for (int k = 0; k < PASSES; ++k) {
+        const uint8_t* p = src0 + (long long)(k * RPP) * pitch;
         lo[k] = __ldg(reinterpret_cast<const uint32_t*>(p));
         hi[k] = __ldg(reinterpret_cast<const uint32_t*>(p + 4));
     }
@@ -309,9 +308,9 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) klt_run_kernel(const KltArgs
             sx0 = (inx - G::MJ) & ~3;
             sy0 = iny - G::MJ;
             const uint8_t* src = Jorigin + (long long)(sy0 + sJ_r) * L.pitch + (sx0 + 4 * sJ_c);
-            const long long step = (long long)G::RPPJ * L.pitch;   // one 64-bit add per pass instead of a widening multiply each
 #pragma unroll
-            for (int k = 0; k < G::PASSJ; ++k, src += step) cp_async4(sJ_dst + k * G::RPPJ * G::PJ, src);
+            for (int k = 0; k < G::PASSJ; ++k)
+                cp_async4(sJ_dst + k * G::RPPJ * G::PJ, src + (long long)(k * G::RPPJ) * L.pitch);
             jstaged = true;
             rsafe = sx0 >= -WW && sx0 + G::DXMAX < L.w && sy0 >= -WH && sy0 + G::DYMAX < L.h;
         };
@@ -489,7 +488,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) klt_run_kernel(const KltArgs
             if (level == 0) st = 0;
             continue;
         }
-        D = __frcp_rn(D);   // == 1.f / D correctly rounded, without the general division sequence
+        D = __fdiv_rn(1.f, D);
 
         // one pass over the window at the staged position of the next image: exact integer sums of diff*Ix, diff*Iy
         // (Newton step) or |diff| (L1 residual); diff = DESCALE(bilinear J, 9) - Iw, the rounding constant rides in the
