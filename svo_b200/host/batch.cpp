@@ -13,7 +13,7 @@ namespace {
 
 [[noreturn]] void raise(svo_gpu_ctx* ctx, const char* where, int rc)
 {
-    throw cv::Exception(std::string(where) + ": svo_gpu error " + std::to_string(rc) + ": " + svo_gpu_last_error(ctx));
+    SVO_THROW(std::string(where) + ": svo_gpu error " + std::to_string(rc) + ": " + svo_gpu_last_error(ctx));
 }
 
 template <typename T>
@@ -47,7 +47,7 @@ SequenceBatch::SequenceBatch(int device, int width, int height, int streams, con
     : w_(width), h_(height), streams_(streams), p_(params)
 {
     if (width < 1 || height < 1 || streams < 1 || params.bucketSize < 1 || params.featuresPerBucket < 1 || params.maxTracks < 0)
-        throw cv::Exception("SequenceBatch: bad geometry or parameters");
+        SVO_THROW("SequenceBatch: bad geometry or parameters");
     bucket_cap_ = (height / params.bucketSize + 1) * (width / params.bucketSize + 1) * params.featuresPerBucket;
     const int max_points = std::max(std::max(32768, width * height / 16), std::max(bucket_cap_, params.maxTracks));
     int rc = svo_gpu_create(&ctx_, device, width, height, std::min(params.maxLevel + 1, SVO_GPU_MAX_LEVELS), max_points, streams);
@@ -88,12 +88,12 @@ void SequenceBatch::reset()
 
 void SequenceBatch::submit(const std::vector<cv::Mat>& frames)
 {
-    if ((int)frames.size() != streams_) throw cv::Exception("SequenceBatch::submit: one frame per sequence expected");
-    if (outstanding() >= SVO_GPU_STEP_DEPTH) throw cv::Exception("SequenceBatch::submit: wait for the oldest frame set first");
+    if ((int)frames.size() != streams_) SVO_THROW("SequenceBatch::submit: one frame per sequence expected");
+    if (outstanding() >= SVO_GPU_STEP_DEPTH) SVO_THROW("SequenceBatch::submit: wait for the oldest frame set first");
     Set& s = *sets_[submitted_ % SVO_GPU_STEP_DEPTH];
     for (int b = 0; b < streams_; ++b) {
         const cv::Mat& m = frames[(size_t)b];
-        if (m.type() != CV_8UC1 || m.cols != w_ || m.rows != h_) throw cv::Exception("SequenceBatch::submit: frames must be CV_8UC1 of the configured size");
+        if (m.type() != CV_8UC1 || m.cols != w_ || m.rows != h_) SVO_THROW("SequenceBatch::submit: frames must be CV_8UC1 of the configured size");
         uint8_t* dst = s.frames + (size_t)b * w_ * h_;
         for (int y = 0; y < h_; ++y) memcpy(dst + (size_t)y * w_, m.data + (size_t)y * m.step, (size_t)w_);
     }
@@ -102,8 +102,8 @@ void SequenceBatch::submit(const std::vector<cv::Mat>& frames)
 
 void SequenceBatch::submit(const uint8_t* frames)
 {
-    if (!frames) throw cv::Exception("SequenceBatch::submit: frames is null");
-    if (outstanding() >= SVO_GPU_STEP_DEPTH) throw cv::Exception("SequenceBatch::submit: wait for the oldest frame set first");
+    if (!frames) SVO_THROW("SequenceBatch::submit: frames is null");
+    if (outstanding() >= SVO_GPU_STEP_DEPTH) SVO_THROW("SequenceBatch::submit: wait for the oldest frame set first");
     Set& s = *sets_[submitted_ % SVO_GPU_STEP_DEPTH];
     svo_gpu_step_params P{};
     P.w = w_; P.h = h_;
@@ -120,7 +120,7 @@ void SequenceBatch::submit(const uint8_t* frames)
 
 void SequenceBatch::wait(std::vector<SequenceResult>& results)
 {
-    if (outstanding() <= 0) throw cv::Exception("SequenceBatch::wait: nothing outstanding");
+    if (outstanding() <= 0) SVO_THROW("SequenceBatch::wait: nothing outstanding");
     Set& s = *sets_[waited_ % SVO_GPU_STEP_DEPTH];
     ++waited_;
     const int rc = svo_gpu_step_wait(ctx_, s.ticket);

@@ -7,8 +7,8 @@
 void FeatureSet::bucketingFeatures(const cv::Mat& image, int bucket_size, int features_per_bucket)
 {
     static_assert(sizeof(cv::Point2f) == 2 * sizeof(float), "Point2f must be two packed floats");
-    if (points.size() != ages.size()) throw cv::Exception("FeatureSet: points and ages differ in length");
-    if (bucket_size < 1) throw cv::Exception("FeatureSet::bucketingFeatures: bucket_size must be >= 1");
+    if (points.size() != ages.size()) SVO_THROW("FeatureSet: points and ages differ in length");
+    if (bucket_size < 1) SVO_THROW("FeatureSet::bucketingFeatures: bucket_size must be >= 1");
     const int n = size();
     // the emission can be longer than the input (aliased cells are emitted twice): size for the worst case
     const long long cells = (long long)(image.rows / bucket_size + 1) * (image.cols / bucket_size + 1);
@@ -22,7 +22,7 @@ void FeatureSet::bucketingFeatures(const cv::Mat& image, int bucket_size, int fe
     if (rc != SVO_GPU_OK) {
         points.resize((size_t)n);
         ages.resize((size_t)n);
-        throw cv::Exception(std::string("svo_gpu_bucket: error ") + std::to_string(rc) + ": " + svo_gpu_last_error(ctx));
+        SVO_THROW(std::string("svo_gpu_bucket: error ") + std::to_string(rc) + ": " + svo_gpu_last_error(ctx));
     }
     points.resize((size_t)n_out);
     ages.resize((size_t)n_out);

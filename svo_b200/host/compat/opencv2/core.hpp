@@ -27,10 +27,19 @@ namespace cv {
 template <typename T> using Ptr = std::shared_ptr<T>;
 template <typename T, typename... A> Ptr<T> makePtr(A&&... a) { return std::make_shared<T>(std::forward<A>(a)...); }
 
+typedef std::string String;
+
+// cv::Exception with OpenCV's constructor (code, err, func, file, line); what() carries the message
 class Exception : public std::runtime_error {
 public:
-    explicit Exception(const std::string& m) : std::runtime_error(m) {}
+    Exception(int code_, const String& err_, const String& func_, const String& file_, int line_)
+        : std::runtime_error(err_ + " (" + func_ + ", " + file_ + ":" + std::to_string(line_) + ")"), code(code_), err(err_),
+          func(func_), file(file_), line(line_) {}
+    int code;
+    String err, func, file;
+    int line;
 };
+namespace Error { enum Code { StsError = -2, StsBadArg = -5 }; }
 
 template <typename T> struct Point_ {
     T x{}, y{};
@@ -113,12 +122,31 @@ private:
     std::shared_ptr<uchar> own_;
 };
 
+// cv::InputArray as far as this boundary needs it: a read-only proxy a cv::Mat converts to implicitly, so that
+// cv::Feature2D::detect has OpenCV's exact signature here too and the wrappers are ONE source for both header sets.
+class _InputArray {
+public:
+    _InputArray() = default;
+    _InputArray(const Mat& m) : m_(&m) {}   // implicit, as in OpenCV
+    Mat getMat(int = -1) const { return m_ ? *m_ : Mat(); }
+    bool empty() const { return !m_ || m_->empty(); }
+
+private:
+    const Mat* m_ = nullptr;
+};
+typedef const _InputArray& InputArray;
+inline InputArray noArray()
+{
+    static const _InputArray none;
+    return none;
+}
+
 // cv::Feature2D as far as the reference uses it: held as cv::Ptr<cv::FeatureDetector> mDetector (include/tracking.h:50),
-// called as mDetector->detect(image, keypoints, mask) (src/tracking.cpp:82).
+// called as mDetector->detect(image, keypoints, mask) (src/tracking.cpp:82).  Same virtual as OpenCV's features2d.hpp.
 class Feature2D {
 public:
     virtual ~Feature2D() = default;
-    virtual void detect(const Mat& image, std::vector<KeyPoint>& keypoints, const Mat& mask = Mat()) = 0;
+    virtual void detect(InputArray image, std::vector<KeyPoint>& keypoints, InputArray mask = noArray()) = 0;
 };
 typedef Feature2D FeatureDetector;
 

@@ -3,6 +3,7 @@
 // holds only the Feature value struct (src/feature.cpp:6-16); its FAST and LK arithmetic are OpenCV calls made from
 // src/tracking.cpp:82, :101-105 and :160-165 -- those are what this file stands in for.  No CPU fallback.
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <string>
@@ -46,7 +47,7 @@ struct CtxEntry {
 struct CtxTable {
     std::map<int, CtxEntry> by_device;
     int device = 0;
-    bool cache = true;
+    bool cache = !(getenv("SVO_FRAME_CACHE") && atoi(getenv("SVO_FRAME_CACHE")) == 0);   // setFrameCache() overrides
     ~CtxTable()
     {
         for (auto& kv : by_device) kv.second.release();
@@ -59,14 +60,14 @@ constexpr int kMaxLevels = SVO_GPU_MAX_LEVELS;
 
 [[noreturn]] void raise(svo_gpu_ctx* ctx, const char* where, int rc)
 {
-    throw cv::Exception(std::string(where) + ": svo_gpu error " + std::to_string(rc) + ": " + svo_gpu_last_error(ctx));
+    SVO_THROW(std::string(where) + ": svo_gpu error " + std::to_string(rc) + ": " + svo_gpu_last_error(ctx));
 }
 
 // gray frames as the reference passes them, or BGR frames straight from cv::imread: the loader's cvtColor
 // (include/async_image_loader.h:68-69) then happens on the device, bit-identical to cv::COLOR_BGR2GRAY
 void check_image(const cv::Mat& m, const char* what)
 {
-    if (m.type() != CV_8UC1 && m.type() != CV_8UC3) throw cv::Exception(std::string(what) + " must be CV_8UC1 or CV_8UC3 (BGR)");
+    if (m.type() != CV_8UC1 && m.type() != CV_8UC3) SVO_THROW(std::string(what) + " must be CV_8UC1 or CV_8UC3 (BGR)");
 }
 
 int upload_image(svo_gpu_ctx* ctx, int slot, const cv::Mat& m)
@@ -233,7 +234,7 @@ void run_fast(const cv::Mat& image, std::vector<cv::KeyPoint>& keypoints, Call&&
 void cvtColorBGR2GRAY(const cv::Mat& bgr, cv::Mat& gray)
 {
     if (bgr.empty()) { gray = cv::Mat(); return; }
-    if (bgr.type() != CV_8UC3) throw cv::Exception("cvtColorBGR2GRAY: source must be CV_8UC3");
+    if (bgr.type() != CV_8UC3) SVO_THROW("cvtColorBGR2GRAY: source must be CV_8UC3");
     CtxEntry& e = entry_for(bgr.cols, bgr.rows, 0);
     const int slot = slot_of(e, bgr);
     cv::Mat out(bgr.rows, bgr.cols, CV_8UC1);   // a fresh buffer: `gray` may be `bgr` itself, as in the loader
@@ -245,8 +246,8 @@ void cvtColorBGR2GRAY(const cv::Mat& bgr, cv::Mat& gray)
 void detectFAST(const cv::Mat& image, std::vector<cv::KeyPoint>& keypoints, const cv::Mat& mask, int threshold, bool nms)
 {
     if (!mask.empty()) {
-        if (mask.type() != CV_8UC1) throw cv::Exception("mask must be CV_8UC1");
-        if (mask.rows != image.rows || mask.cols != image.cols) throw cv::Exception("mask size differs from the image size");
+        if (mask.type() != CV_8UC1) SVO_THROW("mask must be CV_8UC1");
+        if (mask.rows != image.rows || mask.cols != image.cols) SVO_THROW("mask size differs from the image size");
     }
     run_fast(image, keypoints, [&](svo_gpu_ctx* ctx, int slot, float* xy, float* resp, int cap, int* count) {
         return svo_gpu_fast(ctx, slot, threshold, nms ? 1 : 0, mask.empty() ? nullptr : mask.data, mask.step, xy, resp, cap, count);
@@ -269,17 +270,10 @@ cv::Ptr<GpuFastDetector> GpuFastDetector::create(int threshold, bool nonmaxSuppr
     return cv::makePtr<GpuFastDetector>(threshold, nonmaxSuppression);
 }
 
-#ifdef SVO_COMPAT_OPENCV
-void GpuFastDetector::detect(const cv::Mat& image, std::vector<cv::KeyPoint>& keypoints, const cv::Mat& mask)
-{
-    detectFAST(image, keypoints, mask, threshold_, nms_);
-}
-#else
 void GpuFastDetector::detect(cv::InputArray image, std::vector<cv::KeyPoint>& keypoints, cv::InputArray mask)
 {
     detectFAST(image.getMat(), keypoints, mask.empty() ? cv::Mat() : mask.getMat(), threshold_, nms_);
 }
-#endif
 
 // ------------------------------------------------------------------------------------------------ LK
 void calcOpticalFlowPyrLK(const cv::Mat& prevImg, const cv::Mat& nextImg, const std::vector<cv::Point2f>& prevPts,
@@ -296,9 +290,9 @@ void calcOpticalFlowPyrLK(const cv::Mat& prevImg, const cv::Mat& nextImg, const 
     check_image(prevImg, "prevImg");
     check_image(nextImg, "nextImg");
     if (prevImg.empty() || prevImg.rows != nextImg.rows || prevImg.cols != nextImg.cols)
-        throw cv::Exception("calcOpticalFlowPyrLK: prevImg and nextImg must be non-empty and of the same size");
+        SVO_THROW("calcOpticalFlowPyrLK: prevImg and nextImg must be non-empty and of the same size");
     if (maxLevel < 0 || winSize.width <= 2 || winSize.height <= 2)
-        throw cv::Exception("calcOpticalFlowPyrLK: maxLevel >= 0 && winSize.width > 2 && winSize.height > 2");
+        SVO_THROW("calcOpticalFlowPyrLK: maxLevel >= 0 && winSize.width > 2 && winSize.height > 2");
     CtxEntry& e = entry_for(prevImg.cols, prevImg.rows, n);
     svo_gpu_ctx* ctx = e.ctx;
     const int ml = std::min(maxLevel, kMaxLevels - 1);
@@ -331,7 +325,7 @@ void check_pair(const cv::Mat& a, const cv::Mat& b, const char* who)
     check_image(a, who);
     check_image(b, who);
     if (a.empty() || a.rows != b.rows || a.cols != b.cols)
-        throw cv::Exception(std::string(who) + ": the two images must be non-empty and of the same size");
+        SVO_THROW(std::string(who) + ": the two images must be non-empty and of the same size");
 }
 
 }  // namespace
@@ -395,7 +389,7 @@ void filterTracks(const std::vector<cv::Point2f>& a, const std::vector<cv::Point
                   float yThreshold, std::vector<int>& indices)
 {
     const int n = (int)a.size();
-    if (b.size() != a.size() || status.size() != a.size()) throw cv::Exception("filterTracks: a, b and status differ in length");
+    if (b.size() != a.size() || status.size() != a.size()) SVO_THROW("filterTracks: a, b and status differ in length");
     indices.clear();
     if (n == 0) return;
     svo_gpu_ctx* ctx = defaultContext(g_tab.device, 0, 0, n);

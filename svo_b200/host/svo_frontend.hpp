@@ -23,17 +23,10 @@
 
 #include "svo_gpu.h"
 
-namespace svo {
+// failures surface the way a failing OpenCV call does: cv::Exception(code, err, func, file, line)
+#define SVO_THROW(msg) throw cv::Exception(cv::Error::StsError, (msg), __func__, __FILE__, __LINE__)
 
-#ifdef SVO_COMPAT_OPENCV
-typedef const cv::Mat& ImageArg;       // the reference only ever passes cv::Mat here
-inline const cv::Mat& asMat(ImageArg a) { return a; }
-inline cv::Mat noImage() { return cv::Mat(); }
-#else
-typedef cv::InputArray ImageArg;
-inline cv::Mat asMat(ImageArg a) { return a.getMat(); }
-inline cv::InputArray noImage() { return cv::noArray(); }
-#endif
+namespace svo {
 
 // The calling thread's context on `device` (created on first use, grown when a larger image or more points arrive).
 // Tracking::trackFrames is a static member (include/tracking.h:34) with no object to hang state on, hence thread-local.
@@ -63,11 +56,8 @@ class GpuFastDetector : public cv::Feature2D {
 public:
     static cv::Ptr<GpuFastDetector> create(int threshold = 10, bool nonmaxSuppression = true);
     GpuFastDetector(int threshold, bool nonmaxSuppression) : threshold_(threshold), nms_(nonmaxSuppression) {}
-#ifdef SVO_COMPAT_OPENCV
-    void detect(const cv::Mat& image, std::vector<cv::KeyPoint>& keypoints, const cv::Mat& mask = cv::Mat()) override;
-#else
+    // cv::Feature2D::detect's own signature (features2d.hpp), with real OpenCV headers and with the compat ones alike
     void detect(cv::InputArray image, std::vector<cv::KeyPoint>& keypoints, cv::InputArray mask = cv::noArray()) override;
-#endif
     void setThreshold(int t) { threshold_ = t; }
     int getThreshold() const { return threshold_; }
     void setNonmaxSuppression(bool f) { nms_ = f; }

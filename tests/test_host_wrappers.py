@@ -83,7 +83,10 @@ def test_sequence_batch_matches_cpu_pipeline(exe, oracle, tmp_path):
 
 
 @pytest.mark.gpu
-def test_wrappers_match_oracle(exe, oracle, tmp_path):
+@pytest.mark.parametrize("cache", ["1", "0"])
+def test_wrappers_match_oracle(exe, oracle, tmp_path, cache):
+    """cache = the wrappers' content-addressed frame cache (default on; SVO_FRAME_CACHE=0 uploads and rebuilds per call, as
+    cv::calcOpticalFlowPyrLK itself does): same answers either way."""
     w, h, bs, k = 320, 240, 32, 5
     canvas = synth.make_canvas(w, h, 5)
     a, b = synth.render_frame(canvas, w, h, 0), synth.render_frame(canvas, w, h, 1)
@@ -94,7 +97,7 @@ def test_wrappers_match_oracle(exe, oracle, tmp_path):
         a.tofile(f)
         b.tofile(f)
         prev.tofile(f)
-    r = subprocess.run([exe, str(fin), str(fout)], capture_output=True, text=True)
+    r = subprocess.run([exe, str(fin), str(fout)], capture_output=True, text=True, env=dict(os.environ, SVO_FRAME_CACHE=cache))
     assert r.returncode == 0, r.stderr
     buf = open(fout, "rb").read()
     off = 0
