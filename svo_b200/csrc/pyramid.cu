@@ -385,20 +385,51 @@ __global__ void __launch_bounds__(256) pyramid_fused_kernel(const FusedPyrArgs a
                     if (r < G::rw(0) && ln < PW) smem[r * PW + ln] = __funnelshift_r(v[k], nxt, sh);
                 }
             } else if (ln < PW) {
+                // CTA at the frame border.  Whether a word needs BORDER_REFLECT_101 depends on its columns only, so a lane
+                // is "inside" or "border" for all its rows: inside lanes load two aligned words per row, border lanes four
+                // reflected bytes; either way every load of the lane is in flight before the first use (rows in two halves)
+                constexpr int RMAX = (G::rw(0) + 7) / 8, HALF = (RMAX + 1) / 2;
                 const int gx = lox + 4 * ln;
-                for (int r = warp; r < G::rw(0); r += 8) {
-                    const uint8_t* row = src + (size_t)reflect101(loy + r, L.h) * a.raw_pitch;
-                    uint32_t v;
-                    if (gx >= 0 && gx + 7 < L.w) {
-                        const uintptr_t addr = reinterpret_cast<uintptr_t>(row + gx);
-                        const uint32_t* wp = reinterpret_cast<const uint32_t*>(addr & ~(uintptr_t)3);
-                        v = __funnelshift_r(__ldg(wp), __ldg(wp + 1), 8 * (int)(addr & 3));
-                    } else {
-                        v = 0;
+                const bool word_inside = gx >= 0 && gx + 7 < L.w;
+                int cx[4];
 #pragma unroll
-                        for (int b = 0; b < 4; ++b) v |= (uint32_t)__ldg(row + reflect101(gx + b, L.w)) << (8 * b);
+                for (int b = 0; b < 4; ++b) cx[b] = reflect101(gx + b, L.w);
+#pragma unroll
+                for (int h0 = 0; h0 < RMAX; h0 += HALF) {
+                    uint32_t v[HALF];
+                    if (word_inside) {
+                        uint32_t lo[HALF], hi[HALF];
+#pragma unroll
+                        for (int k = 0; k < HALF; ++k) {
+                            const int r = min(warp + 8 * (h0 + k), G::rw(0) - 1);
+                            const uintptr_t addr = reinterpret_cast<uintptr_t>(src + (size_t)reflect101(loy + r, L.h) * a.raw_pitch + gx);
+                            const uint32_t* wp = reinterpret_cast<const uint32_t*>(addr & ~(uintptr_t)3);
+                            lo[k] = __ldg(wp);
+                            hi[k] = __ldg(wp + 1);
+                        }
+#pragma unroll
+                        for (int k = 0; k < HALF; ++k) {
+                            const int r = min(warp + 8 * (h0 + k), G::rw(0) - 1);
+                            const uintptr_t addr = reinterpret_cast<uintptr_t>(src + (size_t)reflect101(loy + r, L.h) * a.raw_pitch + gx);
+                            v[k] = __funnelshift_r(lo[k], hi[k], 8 * (int)(addr & 3));
+                        }
+                    } else {
+                        uint32_t bb[HALF][4];
+#pragma unroll
+                        for (int k = 0; k < HALF; ++k) {
+                            const int r = min(warp + 8 * (h0 + k), G::rw(0) - 1);
+                            const uint8_t* row = src + (size_t)reflect101(loy + r, L.h) * a.raw_pitch;
+#pragma unroll
+                            for (int b = 0; b < 4; ++b) bb[k][b] = __ldg(row + cx[b]);
+                        }
+#pragma unroll
+                        for (int k = 0; k < HALF; ++k) v[k] = bb[k][0] | (bb[k][1] << 8) | (bb[k][2] << 16) | (bb[k][3] << 24);
                     }
-                    smem[r * PW + ln] = v;
+#pragma unroll
+                    for (int k = 0; k < HALF; ++k) {
+                        const int r = warp + 8 * (h0 + k);
+                        if (h0 + k < RMAX && r < G::rw(0)) smem[r * PW + ln] = v[k];
+                    }
                 }
             }
         }
