@@ -32,7 +32,8 @@ def build(force=False):
     """Compile the C restatement (and oracle/_ref when /root/reference is present)."""
     stale = os.path.exists(_LIB) and os.path.getmtime(os.path.join(_HERE, "svo_oracle.c")) > os.path.getmtime(_LIB)
     if force or stale or not os.path.exists(_LIB) or (os.path.isdir("/root/reference/src") and not os.path.exists(_REF)):
-        subprocess.check_call(["make", "-C", _HERE, "-s"])
+        import sys
+        subprocess.check_call(["make", "-C", _HERE, "-s"], stdout=sys.stderr)   # bench.py's stdout carries one JSON line only
 
 
 _lib = None

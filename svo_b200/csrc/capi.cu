@@ -46,6 +46,17 @@ struct StepTicket {
     int batch = 0, kp_cap = 0;
 };
 
+// the captured chain of one step (capi_step.inc), valid for exactly the pointers and settings it was recorded with
+struct StepGraph {
+    cudaGraphExec_t exec = nullptr;
+    svo_gpu_step_params P{};
+    svo_gpu_step_outputs out{};
+    bool has_out = false;
+    int batch = 0, kernels = 0, eff = 0, kp_cap = 0;
+    const void* pyr_prev = nullptr;
+    const void* pyr_cur = nullptr;
+};
+
 thread_local char g_create_error[512] = "";
 
 }  // namespace
@@ -118,8 +129,14 @@ struct svo_gpu_ctx {
     int pyr_async = 1;      // SVO_GPU_STEP_PYR_ASYNC (0 = pyramid on the main stream)
     int pyr_fused = -1;     // SVO_GPU_PYR_FUSED: -1 = per call (fused for small frame sets), 0 = ingest + one pyrDown launch per level, 1 = fused
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    int step_graph = -1;    // SVO_GPU_STEP_GRAPH: -1 = per call (small steps), 0 / 1 = never / whenever possible
+    int steps_since_reset = 0;
+    StepGraph graphs[2][SVO_GPU_STEP_DEPTH];
+    bool out_checked = false, out_checked_ok = false;
+    svo_gpu_step_outputs out_checked_key{};
+    cudaEvent_t ev_klt_int = nullptr;
     int overlap = -1;       // SVO_GPU_STEP_OVERLAP: -1 = per call (detection beside LK when LK does not fill the device), 0 / 1 = never / always
-    int fast_small = 1;     // SVO_GPU_FAST_SMALL: 128-thread FAST CTAs in the step (0 = 256)
+    int fast_small = -1;    // SVO_GPU_FAST_SMALL: FAST CTA size in the step: -1 = by tile count (128 threads, 512 for few tiles), 1 = 128, 0 = 256, 2 = 512
     const uint8_t* pf_ptr = nullptr;   // host pointer of the prefetched frames (nullptr = none pending)
     int pf_slot = -1;
     float stage_ms[4] = {0, 0, 0, 0};
@@ -294,6 +311,7 @@ static int create_buffers(svo_gpu_ctx* ctx)
     CK(cudaEventCreateWithFlags(&ctx->ev_copy, cudaEventDisableTiming));
     CK(cudaStreamCreateWithFlags(&ctx->out_st, cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&ctx->ev_klt, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&ctx->ev_klt_int, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&ctx->ev_out, cudaEventDisableTiming));
     {   // lowest priority: detection CTAs only take what the LK kernel (on st, default priority) leaves free
         int lo = 0, hi = 0;
@@ -312,6 +330,7 @@ static int create_buffers(svo_gpu_ctx* ctx)
     if (const char* v = getenv("SVO_GPU_PYR_FUSED")) ctx->pyr_fused = atoi(v);
     if (const char* v = getenv("SVO_GPU_BUCKET_MODE")) ctx->bb.mode = atoi(v);   // 1: global-memory kernels, 2: one CTA per lane
     if (const char* v = getenv("SVO_GPU_STEP_OVERLAP")) ctx->overlap = atoi(v);
+    if (const char* v = getenv("SVO_GPU_STEP_GRAPH")) ctx->step_graph = atoi(v);
     if (const char* v = getenv("SVO_GPU_FAST_SMALL")) ctx->fast_small = atoi(v);
     CK(cudaStreamSynchronize(ctx->st));
     return 0;
@@ -363,6 +382,10 @@ extern "C" int svo_gpu_destroy(svo_gpu_ctx* ctx)
     if (ctx->ev_copy) cudaEventDestroy(ctx->ev_copy);
     if (ctx->out_st) { cudaStreamSynchronize(ctx->out_st); cudaStreamDestroy(ctx->out_st); }
     if (ctx->ev_klt) cudaEventDestroy(ctx->ev_klt);
+    if (ctx->ev_klt_int) cudaEventDestroy(ctx->ev_klt_int);
+    for (auto& row : ctx->graphs)
+        for (auto& g : row)
+            if (g.exec) cudaGraphExecDestroy(g.exec);
     if (ctx->ev_out) cudaEventDestroy(ctx->ev_out);
     if (ctx->aux_st) { cudaStreamSynchronize(ctx->aux_st); cudaStreamDestroy(ctx->aux_st); }
     if (ctx->pyr_st) { cudaStreamSynchronize(ctx->pyr_st); cudaStreamDestroy(ctx->pyr_st); }
@@ -551,13 +574,13 @@ static int enqueue_pyramid(svo_gpu_ctx* ctx, Slot& s, int win_w, int win_h, int 
     if (int r = ensure(ctx, s.pyr, (size_t)s.g.lane_bytes * (size_t)ctx->max_batch)) return r;
     uint8_t* pyr = static_cast<uint8_t*>(s.pyr.p);
     // One fused launch for levels 0..3 when the frame set is small (its CTAs fit the device about twice over: what counts
-    // there is the chain of dependent launches), the streaming per-level kernels when many lanes fill the device anyway
-    // (measured at 64 lanes: 0.069 ms against 0.117 ms for the fused kernel, whose CTAs spend their time between barriers).
+    // there is the chain of dependent launches), the streaming per-level kernels otherwise (measured: 1 lane 27.6 -> 21.5 us;
+    // 4 lanes the step gets 6 % slower; 64 lanes 0.069 -> 0.117 ms: the fused CTAs spend their time between barriers).
     bool fused = ctx->pyr_fused > 0;
     if (ctx->pyr_fused < 0) {
         int sms = 0;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
-        fused = (long long)((s.w + 63) / 64) * ((s.h + 63) / 64) * s.batch <= 10LL * sms;
+        fused = (long long)((s.w + 63) / 64) * ((s.h + 63) / 64) * s.batch <= 2LL * sms;
     }
     int built = fused ? launch_pyramid_fused(ps, s.raw, s.raw_pitch, s.raw_lane, pyr, s.g, s.batch, &ctx->launches) : 0;
     if (built == 0) {

@@ -334,12 +334,25 @@ void launch_fast(cudaStream_t st, const uint8_t* raw, size_t raw_pitch, size_t r
     }
     static std::atomic<unsigned long long> seen{0};
     if (first_on_device(seen)) {
-        prefer_max_shared(fast_tile_kernel<128>); prefer_max_shared(fast_tile_kernel<256>); prefer_max_shared(fast_gather_kernel);
+        prefer_max_shared(fast_tile_kernel<128>); prefer_max_shared(fast_tile_kernel<256>); prefer_max_shared(fast_tile_kernel<512>);
+        prefer_max_shared(fast_gather_kernel);
     }
     const int ntx = (w + TW - 1) / TW;
     dim3 grid(ntx, (h + TH - 1) / TH, batch);
-    if (small_ctas)   // the default: 128-thread CTAs measured 2 % faster than 256 (and 64 slower), gpurun_out/s11, s12
+    // CTA size: 128 threads when the tiles fill the device several times over (measured 2 % faster than 256, and 64 slower:
+    // gpurun_out/s11, s12); with few tiles (one stream = 120) the kernel's time is one CTA's, so the tile is spread over 512
+    // threads instead (small_ctas: 1 = 128, 0 = 256, 2 = 512, -1 = by tile count)
+    if (small_ctas < 0) {
+        int dev = 0, sms = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        small_ctas = (long long)grid.x * grid.y * grid.z <= 2LL * sms ? 2 : 1;
+    }
+    if (small_ctas == 1)
         fast_tile_kernel<128><<<grid, 128, 0, st>>>(raw, raw_pitch, raw_lane, w, h, threshold, nms, mask, mask_pitch, mask_lane,
+                                                    fb, ntx, mp);
+    else if (small_ctas == 2)
+        fast_tile_kernel<512><<<grid, 512, 0, st>>>(raw, raw_pitch, raw_lane, w, h, threshold, nms, mask, mask_pitch, mask_lane,
                                                     fb, ntx, mp);
     else
         fast_tile_kernel<256><<<grid, 256, 0, st>>>(raw, raw_pitch, raw_lane, w, h, threshold, nms, mask, mask_pitch, mask_lane,

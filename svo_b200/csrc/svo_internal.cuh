@@ -102,7 +102,7 @@ struct FastMaskPts {
 // mask: device u8 plane per lane (pitch mask_pitch, lane stride mask_lane) or nullptr; mask_pts: see above (either, or none)
 void launch_fast(cudaStream_t st, const uint8_t* raw, size_t raw_pitch, size_t raw_lane, int w, int h, int threshold,
                  int nms, const uint8_t* mask, size_t mask_pitch, size_t mask_lane, const FastBufs& fb, int batch,
-                 long long* launches, int small_ctas = 1, const FastMaskPts* mask_pts = nullptr);
+                 long long* launches, int small_ctas = -1, const FastMaskPts* mask_pts = nullptr);
 
 // ------------------------------------------------------------------------------------------------ bucket.cu
 struct BucketBufs {

@@ -135,13 +135,17 @@ def test_step_pipelined_ingest(oracle):
                     _check_lane(fe, b, cpus[b].step(seqs[b, t]), first=(t == 0))
 
 
+@pytest.mark.parametrize("graph", ["1", "0"])
 @pytest.mark.parametrize("mem", ["host", "device"])
-def test_step_submit_wait(oracle, mem):
+def test_step_submit_wait(oracle, mem, graph, monkeypatch):
     """svo_gpu_step_submit / svo_gpu_step_wait with two steps outstanding (submit(t + 1) before wait(t)): each step's
-    results, read after ITS wait, equal the synchronous CPU pipeline; host frames are prefetched one step ahead."""
+    results, read after ITS wait, equal the synchronous CPU pipeline; host frames are prefetched one step ahead.
+    SVO_GPU_STEP_GRAPH=1: from the third step on the chain LK .. counts is a captured CUDA graph, replayed per step (its
+    ev_klt an external event-record node the next step's pyramid build waits for); 0: every step enqueued call by call."""
     import torch
     from oracle.cpu_pipeline import CpuFrontend
-    seqs = _seqs(6)
+    monkeypatch.setenv("SVO_GPU_STEP_GRAPH", graph)
+    seqs = _seqs(9)
     B, T = seqs.shape[0], seqs.shape[1]
     frames = torch.from_numpy(np.ascontiguousarray(seqs.transpose(1, 0, 2, 3)))           # [t, lane, h, w]
     frames = frames.pin_memory() if mem == "host" else frames.cuda()
@@ -166,6 +170,8 @@ def test_step_submit_wait(oracle, mem):
             check(t - 1)
         check(T - 1)
         assert fe.outstanding == 0 and ctx.last_klt_iterations > 0
+        # launches are counted the same way replayed or enqueued
+        assert ctx.launch_count > 0
 
 
 def test_step_submit_wait_errors():
