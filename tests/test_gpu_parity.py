@@ -92,6 +92,20 @@ def test_fast_mask(ctx, oracle, c1_frames):
     assert np.array_equal(xy3, oxy)
 
 
+@pytest.mark.parametrize("cta", ["1", "0", "2"])
+def test_fast_cta_sizes(oracle, c1_frames, monkeypatch, cta):
+    """SVO_GPU_FAST_SMALL forces the FAST CTA size (1 = 128 threads, 0 = 256, 2 = 512; unset = by tile count): same list."""
+    img = c1_frames[0]
+    h, w = img.shape
+    pts = np.random.default_rng(4).uniform([0, 0], [w, h], size=(800, 2)).astype(np.float32)
+    monkeypatch.setenv("SVO_GPU_FAST_SMALL", cta)
+    with capi.Context(max_w=w, max_h=h, max_levels=4, max_points=65536, max_batch=1) as c:
+        c.upload(0, img)
+        xy, resp = c.fast_masked_by_points(0, pts, 10.0, 20, True)
+    oxy, oresp = oracle.orc_fast(img, 20, True, mask=oracle.orc_build_mask(w, h, pts, 10.0))
+    assert len(oxy) > 1000 and np.array_equal(xy, oxy) and np.array_equal(resp, oresp)
+
+
 def test_fast_capacity_error(ctx, c1_frames):
     ctx.upload(0, c1_frames[0])
     with pytest.raises(capi.SvoGpuError) as e:
