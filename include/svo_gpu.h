@@ -39,7 +39,7 @@ extern "C" {
 #define SVO_GPU_E_UNSUPPORTED (-4) /* valid for OpenCV, not implemented here (OPTFLOW_USE_INITIAL_FLOW, window > 45) */
 #define SVO_GPU_E_STATE (-5)       /* slot not uploaded / pyramid not built (or built for a smaller window) */
 
-#define SVO_GPU_NUM_SLOTS 4
+#define SVO_GPU_NUM_SLOTS 5
 #define SVO_GPU_STEP_DEPTH 2   /* steps that may be outstanding between svo_gpu_step_submit and svo_gpu_step_wait */
 #define SVO_GPU_MAX_LEVELS 8       /* pyramid levels 0..7 (OpenCV maxLevel <= 7) */
 #define SVO_GPU_MAX_WIN 45         /* largest LK window side */
@@ -266,7 +266,8 @@ typedef struct svo_gpu_step_outputs {
 /* One frame of `batch` independent streams: ingest images[b] (host or device memory), build its pyramid, run LK from
  * each lane's previous frame on that lane's current tracks, run FAST (+ tracked-points mask) on the new frame, bucket
  * the detections, and make the first max_tracks of them the lane's tracks for the next call.  The context ping-pongs
- * two slots internally (SVO_GPU_NUM_SLOTS-2 and -1).  Lanes never interact; this is how independent sequences share one
+ * a ring of three slots internally (SVO_GPU_NUM_SLOTS-3 .. -1: this frame, the previous one, and a free
+ * one for the next frame's copy and pyramid build).  Lanes never interact; this is how independent sequences share one
  * GPU (and, with one context per device, several GPUs). */
 SVO_GPU_API int svo_gpu_step(svo_gpu_ctx* ctx, const uint8_t* images, int mem_kind, size_t stride_bytes,
                              size_t image_stride_bytes, int batch, const svo_gpu_step_params* params,

@@ -13,7 +13,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("SVO_GPU_LIB") or os.path.join(_HERE, "lib", "libsvo_gpu.so")
 
 OK, E_ARG, E_CAPACITY, E_CUDA, E_UNSUPPORTED, E_STATE = 0, -1, -2, -3, -4, -5
-NUM_SLOTS = 4
+NUM_SLOTS = 5
 TC_COUNT, TC_EPS = 1, 2
 LK_USE_INITIAL_FLOW, LK_GET_MIN_EIGENVALS = 4, 8
 MEM_HOST, MEM_DEVICE = 0, 1

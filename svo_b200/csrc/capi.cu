@@ -57,6 +57,8 @@ struct StepGraph {
     const void* pyr_cur = nullptr;
 };
 
+constexpr int kStepBase = SVO_GPU_NUM_SLOTS - 3;   // svo_gpu_step's ring of three slots
+
 thread_local char g_create_error[512] = "";
 
 }  // namespace
@@ -107,14 +109,14 @@ struct svo_gpu_ctx {
 
     // svo_gpu_step state
     bool step_has_prev = false;
-    int step_cur = SVO_GPU_NUM_SLOTS - 2;
+    int step_cur = kStepBase;
     svo_gpu_step_params step_params{};
     int step_batch = 0;
     bool profile = false;
     StepTicket tickets[SVO_GPU_STEP_DEPTH];
     int next_ticket = 0;
     int kp_hint = 0;              // keypoints per lane seen by the last completed step (+25 %), 0 = unknown
-    cudaEvent_t ev_raw_free[2] = {nullptr, nullptr};   // per step slot: the ingest that last read its raw frame is through
+    cudaEvent_t ev_raw_free[3] = {nullptr, nullptr, nullptr};   // per step slot: the ingest that last read its raw frame is through
     // frame ingest pipelining: the next step's host frames are copied on a second stream while this step computes
     cudaStream_t copy_st = nullptr;
     cudaEvent_t ev_copy = nullptr;
@@ -131,10 +133,9 @@ struct svo_gpu_ctx {
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     int step_graph = -1;    // SVO_GPU_STEP_GRAPH: -1 = per call (small steps), 0 / 1 = never / whenever possible
     int steps_since_reset = 0;
-    StepGraph graphs[2][SVO_GPU_STEP_DEPTH];
+    StepGraph graphs[3][SVO_GPU_STEP_DEPTH];
     bool out_checked = false, out_checked_ok = false;
     svo_gpu_step_outputs out_checked_key{};
-    cudaEvent_t ev_klt_int = nullptr;
     int overlap = -1;       // SVO_GPU_STEP_OVERLAP: -1 = per call (detection beside LK when LK does not fill the device), 0 / 1 = never / always
     int fast_small = -1;    // SVO_GPU_FAST_SMALL: FAST CTA size in the step: -1 = by tile count (128 threads, 512 for few tiles), 1 = 128, 0 = 256, 2 = 512
     const uint8_t* pf_ptr = nullptr;   // host pointer of the prefetched frames (nullptr = none pending)
@@ -311,7 +312,6 @@ static int create_buffers(svo_gpu_ctx* ctx)
     CK(cudaEventCreateWithFlags(&ctx->ev_copy, cudaEventDisableTiming));
     CK(cudaStreamCreateWithFlags(&ctx->out_st, cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&ctx->ev_klt, cudaEventDisableTiming));
-    CK(cudaEventCreateWithFlags(&ctx->ev_klt_int, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&ctx->ev_out, cudaEventDisableTiming));
     {   // lowest priority: detection CTAs only take what the LK kernel (on st, default priority) leaves free
         int lo = 0, hi = 0;
@@ -382,7 +382,6 @@ extern "C" int svo_gpu_destroy(svo_gpu_ctx* ctx)
     if (ctx->ev_copy) cudaEventDestroy(ctx->ev_copy);
     if (ctx->out_st) { cudaStreamSynchronize(ctx->out_st); cudaStreamDestroy(ctx->out_st); }
     if (ctx->ev_klt) cudaEventDestroy(ctx->ev_klt);
-    if (ctx->ev_klt_int) cudaEventDestroy(ctx->ev_klt_int);
     for (auto& row : ctx->graphs)
         for (auto& g : row)
             if (g.exec) cudaGraphExecDestroy(g.exec);
