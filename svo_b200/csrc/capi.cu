@@ -88,7 +88,7 @@ struct svo_gpu_ctx {
     uint8_t* trk_status = nullptr;
     float* trk_err = nullptr;
     int* trk_n = nullptr;         // [B]
-    int* step_summary = nullptr;  // [5][B] keypoints, bucketed, bucket error flags, key-frame flags, survivors of the step (one
+    int* step_summary = nullptr;  // [6][B] tracked, keypoints, bucketed, bucket error flags, key-frame flags, survivors of the step (one
                                   // read-back) + [B] arrival counters of next_tracks_kernel (zero between launches)
     int* lane_kf = nullptr;       // [B] carry_tracks mode: the lane's frame being processed is a key-frame
     int* int_max = nullptr;       // [B] all INT_MAX: "n is given by n_max" for the host-pointer calls
@@ -280,7 +280,7 @@ static int create_buffers(svo_gpu_ctx* ctx)
     if (int r = dmalloc(ctx, ctx->trk_err, B * NP)) return r;
     if (int r = dmalloc(ctx, ctx->trk_n, B)) return r;
     if (int r = dmalloc(ctx, ctx->int_max, B)) return r;
-    if (int r = dmalloc(ctx, ctx->step_summary, 6 * B)) return r;
+    if (int r = dmalloc(ctx, ctx->step_summary, 7 * B)) return r;
     if (int r = dmalloc(ctx, ctx->lane_kf, B)) return r;
     if (int r = dmalloc(ctx, ctx->d_iters, 2)) return r;   // [0] LK iterations, [1] LK work counter
     if (int r = dmalloc(ctx, ctx->flt_index, B * NP)) return r;
@@ -290,7 +290,7 @@ static int create_buffers(svo_gpu_ctx* ctx)
     if (int r = dmalloc(ctx, ctx->flt_n, B)) return r;
     CK(cudaMemsetAsync(ctx->trk_n, 0, sizeof(int) * B, ctx->st));
     CK(cudaMemsetAsync(ctx->flt_n, 0, sizeof(int) * B, ctx->st));
-    CK(cudaMemsetAsync(ctx->step_summary, 0, sizeof(int) * 6 * B, ctx->st));
+    CK(cudaMemsetAsync(ctx->step_summary, 0, sizeof(int) * 7 * B, ctx->st));
     CK(cudaMemsetAsync(ctx->d_iters, 0, sizeof(unsigned long long), ctx->st));
     {
         std::vector<int> big(B, INT_MAX);
