@@ -131,7 +131,7 @@ struct svo_gpu_ctx {
     int pyr_async = 1;      // SVO_GPU_STEP_PYR_ASYNC (0 = pyramid on the main stream)
     int pyr_fused = -1;     // SVO_GPU_PYR_FUSED: -1 = per call (fused for small frame sets), 0 = ingest + one pyrDown launch per level, 1 = fused
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
-    int step_graph = -1;    // SVO_GPU_STEP_GRAPH: -1 = per call (small steps), 0 / 1 = never / whenever possible
+    int step_graph = 1;     // SVO_GPU_STEP_GRAPH: 1 = the step's chain is captured and replayed whenever possible (default), 0 = never, -1 = small steps only
     int steps_since_reset = 0;
     StepGraph graphs[3][SVO_GPU_STEP_DEPTH];
     bool out_checked = false, out_checked_ok = false;

@@ -138,3 +138,43 @@ def test_c5_split_over_two_contexts(frames, gpu64):
                         continue
                     for name in arrs:
                         assert np.array_equal(a[name][j, :n], b[name][s, :n]), (name, rank, s, t)
+
+
+def test_graph_replay_at_bench_shape(frames, monkeypatch):
+    """The step's chain replayed from captured CUDA graphs (default; six variants, all replayed from the 9th step on) against
+    the same steps enqueued call by call (SVO_GPU_STEP_GRAPH=0), 64 lanes, 14 steps cycling the fixture's frames: every
+    output of every lane and step bit-identical, and the same number of kernels counted."""
+    import torch
+    cells = (H // WL["bucket_size"] + 1) * (W // WL["bucket_size"] + 1) * WL["per_bucket"]
+    host = torch.from_numpy(frames).pin_memory()
+    runs = {}
+    for graph in ("0", "1"):
+        monkeypatch.setenv("SVO_GPU_STEP_GRAPH", graph)
+        with capi.Context(max_w=W, max_h=H, max_levels=4, max_points=32768, max_batch=S) as ctx:
+            fe = Frontend(ctx, W, H, S, kp_capacity=KP_CAP, bucket_capacity=cells, **_params())
+            res = []
+
+            def collect():
+                fe.wait()
+                res.append({k: getattr(fe, k).copy() for k in ("n_tracked", "n_keypoints", "n_bucketed", "next_xy", "status", "err",
+                                                             "kp_xy", "kp_response", "bucket_xy")})
+
+            for t in range(14):
+                fe.submit(host[t % T].data_ptr(), host[(t + 1) % T].data_ptr(), capi.MEM_HOST, W, W * H)
+                if fe.outstanding == 2:
+                    collect()
+            while fe.outstanding:
+                collect()
+            runs[graph] = (res, ctx.launch_count)
+    (a, la), (b, lb) = runs["0"], runs["1"]
+    assert la == lb and len(a) == len(b) == 14
+    for t in range(14):
+        for cnt, arrs in (("n_tracked", ("next_xy", "status", "err")), ("n_keypoints", ("kp_xy", "kp_response")),
+                          ("n_bucketed", ("bucket_xy",))):
+            assert np.array_equal(a[t][cnt], b[t][cnt]), (t, cnt)
+            if cnt == "n_tracked" and t == 0:
+                continue
+            for s in range(S):
+                n = int(a[t][cnt][s])
+                for name in arrs:
+                    assert np.array_equal(a[t][name][s, :n], b[t][name][s, :n]), (t, s, name)
