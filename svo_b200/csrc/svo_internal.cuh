@@ -73,7 +73,10 @@ void launch_pyrdown(cudaStream_t st, uint8_t* pyr, const PyrGeom& g, int level, 
 
 // ------------------------------------------------------------------------------------------------ fast.cu
 constexpr int kFastTW = 128;  // tile width: one (row, tile) segment holds at most 128 keypoints
-constexpr int kFastTH = 32;
+#ifndef SVO_FAST_TH
+#define SVO_FAST_TH 32   // tile height: 64 measured against 32 in profiles/r02_s_fast_tiles.txt
+#endif
+constexpr int kFastTH = SVO_FAST_TH;
 
 struct FastBufs {
     // per lane strides are in elements of the respective type
