@@ -136,7 +136,7 @@ struct svo_gpu_ctx {
     StepGraph graphs[3][SVO_GPU_STEP_DEPTH];
     bool out_checked = false, out_checked_ok = false;
     svo_gpu_step_outputs out_checked_key{};
-    int overlap = -1;       // SVO_GPU_STEP_OVERLAP: -1 = per call (detection beside LK when LK does not fill the device), 0 / 1 = never / always
+    int overlap = 1;        // SVO_GPU_STEP_OVERLAP: 1 = detection beside LK (default: measured faster at every stream count), 0 = back to back, -1 = only when LK does not fill the device
     int fast_small = -1;    // SVO_GPU_FAST_SMALL: FAST CTA size in the step: -1 = by tile count (128 threads, 512 for few tiles), 1 = 128, 0 = 256, 2 = 512
     const uint8_t* pf_ptr = nullptr;   // host pointer of the prefetched frames (nullptr = none pending)
     int pf_slot = -1;
