@@ -39,7 +39,6 @@ struct StepTicket {
     int* hs = nullptr;            // pinned, 6 * max_batch + 16 ints: tracked, keypoints, bucketed, bucket error flags, key-frame flags, survivors, LK iterations
     cudaEvent_t done = nullptr;
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
-    cudaEvent_t eva[4] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t evk = nullptr;    // main stream, in front of LK (the pyramid may have been built on another stream, earlier)
     svo_gpu_step_outputs out{};
     bool has_out = false, prof = false, track = false, overlap = false;
@@ -304,7 +303,6 @@ static int create_buffers(svo_gpu_ctx* ctx)
         CK(cudaMallocHost(reinterpret_cast<void**>(&tk.hs), sizeof(int) * (6 * B + 16)));
         CK(cudaEventCreateWithFlags(&tk.done, cudaEventDisableTiming));
         for (auto& e : tk.ev) CK(cudaEventCreate(&e));
-        for (auto& e : tk.eva) CK(cudaEventCreate(&e));
         CK(cudaEventCreate(&tk.evk));
     }
     for (auto& e : ctx->ev_raw_free) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -395,7 +393,6 @@ extern "C" int svo_gpu_destroy(svo_gpu_ctx* ctx)
         if (tk.hs) cudaFreeHost(tk.hs);
         if (tk.done) cudaEventDestroy(tk.done);
         for (auto& e : tk.ev) if (e) cudaEventDestroy(e);
-        for (auto& e : tk.eva) if (e) cudaEventDestroy(e);
         if (tk.evk) cudaEventDestroy(tk.evk);
     }
     for (auto& e : ctx->ev_raw_free) if (e) cudaEventDestroy(e);

@@ -49,18 +49,19 @@ def test_step_matches_cpu_pipeline(oracle, mask_half):
 
 @pytest.mark.parametrize("overlap", ["1", "0"])
 def test_step_detection_beside_tracking(oracle, monkeypatch, overlap):
-    """SVO_GPU_STEP_OVERLAP (read by svo_gpu_create): 1 = FAST -> bucketing on a second stream beside the LK kernel, 0 = back to
-    back on one stream (unset, as in every other test: decided per call -- these three small lanes overlap).  Same answers,
-    and the profiled stage times stay meaningful."""
+    """SVO_GPU_STEP_OVERLAP (read by svo_gpu_create): 1 (the default, as in every other test) = FAST -> bucketing on a second
+    stream beside the LK kernel, 0 = back to back on one stream.  Same answers.  The last steps are profiled: a profiled step
+    always runs its stages back to back, so that each bracket holds one stage."""
     from oracle.cpu_pipeline import CpuFrontend
     monkeypatch.setenv("SVO_GPU_STEP_OVERLAP", overlap)
-    seqs = _seqs()
+    seqs = _seqs(6)
     B = seqs.shape[0]
     with capi.Context(max_w=W, max_h=H, max_levels=4, max_points=8192, max_batch=B) as ctx:
         fe = Frontend(ctx, W, H, B, kp_capacity=8192, bucket_capacity=2048, max_tracks=400, mask_half=10.0)
         cpus = [CpuFrontend(fe.pdict, impl="orc") for _ in range(B)]
-        ctx.step_profile(True)
         for t in range(seqs.shape[1]):
+            if t == 4:
+                ctx.step_profile(True)
             fe.step_host(np.ascontiguousarray(seqs[:, t]))
             for b in range(B):
                 _check_lane(fe, b, cpus[b].step(seqs[b, t]), first=(t == 0))
