@@ -388,9 +388,9 @@ def run_b200(args):
     def submit_host(i):
         fe.submit(hptr(i), hptr(i + 1), capi.MEM_HOST, w, w * h)
 
-    # Untimed steps in front of each timed loop: the W asked for, and at least 9, because the library captures the step's chain
-    # into CUDA graphs during the first 8 steps of a loop (six variants: 3 frame slots x 2 tickets); capture is set-up, not work.
-    WU = max(W, 9)
+    # Untimed steps in front of each timed loop: the W asked for, and at least 4, because the library records the step's chain
+    # into CUDA graphs during steps 2 and 3 of a loop (six variants: 3 frame slots x 2 tickets); capture is set-up, not work.
+    WU = max(W, 4)
     fe.reset()
     run_steps(0, WU, submit_host)
     barrier()

@@ -133,8 +133,9 @@ struct svo_gpu_ctx {
     int step_graph = 1;     // SVO_GPU_STEP_GRAPH: 1 = the step's chain is captured and replayed whenever possible (default), 0 = never, -1 = small steps only
     int steps_since_reset = 0;
     StepGraph graphs[3][SVO_GPU_STEP_DEPTH];
-    bool out_checked = false, out_checked_ok = false;
-    svo_gpu_step_outputs out_checked_key{};
+    bool graphs_precaptured = false;
+    bool out_checked[SVO_GPU_STEP_DEPTH] = {}, out_checked_ok[SVO_GPU_STEP_DEPTH] = {};
+    svo_gpu_step_outputs out_checked_key[SVO_GPU_STEP_DEPTH] = {};
     int overlap = 1;        // SVO_GPU_STEP_OVERLAP: 1 = detection beside LK (default: measured faster at every stream count), 0 = back to back, -1 = only when LK does not fill the device
     int fast_small = -1;    // SVO_GPU_FAST_SMALL: FAST CTA size in the step: -1 = by tile count (128 threads, 512 for few tiles), 1 = 128, 0 = 256, 2 = 512
     const uint8_t* pf_ptr = nullptr;   // host pointer of the prefetched frames (nullptr = none pending)

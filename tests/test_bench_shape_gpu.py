@@ -141,7 +141,7 @@ def test_c5_split_over_two_contexts(frames, gpu64):
 
 
 def test_graph_replay_at_bench_shape(frames, monkeypatch):
-    """The step's chain replayed from captured CUDA graphs (default; six variants, all replayed from the 9th step on) against
+    """The step's chain replayed from captured CUDA graphs (default; six variants, recorded during steps 2 and 3, replayed from then on) against
     the same steps enqueued call by call (SVO_GPU_STEP_GRAPH=0), 64 lanes, 14 steps cycling the fixture's frames: every
     output of every lane and step bit-identical, and the same number of kernels counted."""
     import torch
