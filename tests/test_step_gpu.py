@@ -241,3 +241,31 @@ def test_step_capacity_error():
         with pytest.raises(capi.SvoGpuError) as e:
             fe.step_host(np.ascontiguousarray(seqs[:, 0]))
         assert e.value.code == capi.E_CAPACITY
+
+
+def test_step_with_pageable_outputs(oracle, monkeypatch):
+    """Result arrays in ordinary (pageable) host memory: device-to-host copies into them cannot be captured, so the step keeps
+    enqueueing call by call instead of replaying a graph -- same answers, two steps outstanding."""
+    from oracle.cpu_pipeline import CpuFrontend
+    from svo_b200 import frontend
+    monkeypatch.setattr(frontend, "_pinned", lambda shape, dtype: (np.empty(shape, dtype), None))
+    seqs = _seqs(7)
+    B, T = seqs.shape[0], seqs.shape[1]
+    frames = np.ascontiguousarray(seqs.transpose(1, 0, 2, 3))
+    with capi.Context(max_w=W, max_h=H, max_levels=4, max_points=8192, max_batch=B) as ctx:
+        fe = Frontend(ctx, W, H, B, kp_capacity=8192, bucket_capacity=2048, max_tracks=400, mask_half=10.0)
+        cpus = [CpuFrontend(fe.pdict, impl="orc") for _ in range(B)]
+        done = 0
+        for t in range(T):
+            fe.submit(frames[t].ctypes.data, None, capi.MEM_HOST, W, W * H)
+            if fe.outstanding == 2:
+                fe.wait()
+                for b in range(B):
+                    _check_lane(fe, b, cpus[b].step(seqs[b, done]), first=(done == 0))
+                done += 1
+        while fe.outstanding:
+            fe.wait()
+            for b in range(B):
+                _check_lane(fe, b, cpus[b].step(seqs[b, done]), first=(done == 0))
+            done += 1
+        assert done == T
