@@ -30,7 +30,7 @@ T* pinned(size_t n)
 // page-locked frame staging and result arrays of one outstanding frame set
 struct SequenceBatch::Set {
     uint8_t* frames = nullptr;
-    int *n_tracked = nullptr, *n_keypoints = nullptr, *n_bucketed = nullptr;
+    int *n_tracked = nullptr, *n_keypoints = nullptr, *n_bucketed = nullptr, *keyframe = nullptr, *n_survived = nullptr, *survivor_index = nullptr;
     float *next_xy = nullptr, *err = nullptr, *bucket_xy = nullptr;
     uint8_t* status = nullptr;
     svo_gpu_step_outputs out{};
@@ -38,7 +38,7 @@ struct SequenceBatch::Set {
     ~Set()
     {
         for (void* p : {(void*)frames, (void*)n_tracked, (void*)n_keypoints, (void*)n_bucketed, (void*)next_xy, (void*)err,
-                        (void*)bucket_xy, (void*)status})
+                        (void*)bucket_xy, (void*)status, (void*)keyframe, (void*)n_survived, (void*)survivor_index})
             svo_gpu_host_free(p);
     }
 };
@@ -60,6 +60,8 @@ SequenceBatch::SequenceBatch(int device, int width, int height, int streams, con
             s->n_tracked = pinned<int>(S); s->n_keypoints = pinned<int>(S); s->n_bucketed = pinned<int>(S);
             s->next_xy = pinned<float>(S * T * 2); s->status = pinned<uint8_t>(S * T); s->err = pinned<float>(S * T);
             s->bucket_xy = pinned<float>(S * Bc * 2);
+            s->keyframe = pinned<int>(S); s->n_survived = pinned<int>(S); s->survivor_index = pinned<int>(S * T);
+            s->out.keyframe = s->keyframe; s->out.n_survived = s->n_survived; s->out.survivor_index = s->survivor_index;
             s->out.n_tracked = s->n_tracked; s->out.n_keypoints = s->n_keypoints; s->out.n_bucketed = s->n_bucketed;
             s->out.next_xy = s->next_xy; s->out.status = s->status; s->out.err = s->err;
             s->out.track_capacity = (int)T;
@@ -112,6 +114,7 @@ void SequenceBatch::submit(const uint8_t* frames)
     P.win_w = p_.winSize.width; P.win_h = p_.winSize.height; P.max_level = p_.maxLevel;
     P.max_count = p_.criteria.maxCount; P.epsilon = p_.criteria.epsilon; P.criteria_type = p_.criteria.type;
     P.flags = p_.flags; P.min_eig_threshold = p_.minEigThreshold;
+    P.carry_tracks = p_.carryTracks ? 1 : 0; P.features_to_track = p_.featuresToTrack;
     const int rc = svo_gpu_step_submit(ctx_, frames, nullptr, SVO_GPU_MEM_HOST, (size_t)w_, (size_t)w_ * h_, streams_, &P,
                                        &s.out, &s.ticket);
     if (rc != SVO_GPU_OK) raise(ctx_, "svo_gpu_step_submit", rc);
@@ -137,6 +140,9 @@ void SequenceBatch::wait(std::vector<SequenceResult>& results)
         const cv::Point2f* bx = reinterpret_cast<const cv::Point2f*>(s.bucket_xy) + (size_t)b * Bc;
         r.features.assign(bx, bx + nb);
         r.keypoints = s.n_keypoints[b];
+        r.keyframe = !p_.carryTracks || s.keyframe[b] != 0;
+        r.survivors.clear();
+        if (p_.carryTracks) r.survivors.assign(s.survivor_index + (size_t)b * T, s.survivor_index + (size_t)b * T + (size_t)s.n_survived[b]);
     }
 }
 

@@ -163,7 +163,9 @@ int main(int argc, char** argv)
         fprintf(stderr, "detect() returned without a GPU: a CPU fallback must not exist\n");
         return 1;
     }
-    if (argc == 4 && !strcmp(argv[1], "--batch")) {
+    if ((argc == 4 || argc == 5) && !strcmp(argv[1], "--batch")) {
+        // optional 4th argument: features_to_track -> the reference's own track policy (FrontendParams::carryTracks); each
+        // stream's record then ends with its key-frame flag and its survivor indices
         // svo::SequenceBatch the way a many-sequence driver uses it: frame set t + 1 is submitted before set t is waited for.
         // in.bin = int32 {w, h, streams, frames, max_tracks}, then frames x streams images; out.bin = per frame, per stream:
         // n_tracked, tracked xy, status, err, n_features, features xy, keypoints
@@ -183,6 +185,7 @@ int main(int argc, char** argv)
         try {
             svo::FrontendParams fp;
             fp.maxTracks = hdr[4];
+            if (argc == 5) { fp.carryTracks = true; fp.featuresToTrack = atoi(argv[4]); }
             svo::SequenceBatch batch(0, w, h, S, fp);
             std::vector<svo::SequenceResult> res;
             auto dump = [&]() {
@@ -195,6 +198,11 @@ int main(int argc, char** argv)
                     put_i(fo, (int)r.features.size());
                     put(fo, r.features.data(), 8 * r.features.size());
                     put_i(fo, r.keypoints);
+                    if (argc == 5) {
+                        put_i(fo, r.keyframe ? 1 : 0);
+                        put_i(fo, (int)r.survivors.size());
+                        put(fo, r.survivors.data(), 4 * r.survivors.size());
+                    }
                 }
             };
             batch.submit(seq[0]);

@@ -124,6 +124,12 @@ struct FrontendParams {
     cv::TermCriteria criteria = cv::TermCriteria(cv::TermCriteria::COUNT + cv::TermCriteria::EPS, 50, 0.001);   // :157
     int flags = cv::OPTFLOW_LK_GET_MIN_EIGENVALS;                                                              // :164
     double minEigThreshold = 1e-4;
+    // false: every frame is a key-frame and a sequence's tracks are re-seeded from its bucketed detections (fixed load).
+    // true: the reference's own policy -- LK survivors carry over (src/tracking.cpp:168-177), detection runs only on
+    // key-frames (a sequence's first frame, or after a non-key-frame that ended below featuresToTrack, :69-70), new features
+    // are appended after the survivors (:254).  Decided per sequence on the device.
+    bool carryTracks = false;
+    int featuresToTrack = 70;         // configs/config.yaml:15
 };
 
 struct SequenceResult {
@@ -132,6 +138,11 @@ struct SequenceResult {
     std::vector<float> err;
     std::vector<cv::Point2f> features;  // bucketed detections of this frame; the first maxTracks are the next frame's tracks
     int keypoints = 0;                  // FAST keypoints found before bucketing
+    // carryTracks only: was this frame a key-frame (did detection run), and for each LK survivor its position in `tracked`
+    // (= in the track list the frame started with), so that Feature::mapPoint bindings carry over (src/tracking.cpp:171);
+    // the next frame's track list is the survivors' `tracked` entries followed by the head of `features`
+    bool keyframe = true;
+    std::vector<int> survivors;
 };
 
 class SequenceBatch {

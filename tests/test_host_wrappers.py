@@ -175,3 +175,48 @@ def test_frame_cache_uploads_and_builds_each_frame_once(exe, tmp_path):
     assert d["host_mask"]["keypoints_per_frame"] == d["device_mask"]["keypoints_per_frame"]
     rep = d["repeat_call"]
     assert rep == {"launches": 2, "uploads": 0, "pyramids": 0, "hits": 4}, rep
+
+
+@pytest.mark.gpu
+def test_sequence_batch_reference_track_policy(exe, oracle, tmp_path):
+    """svo::SequenceBatch with FrontendParams::carryTracks (the reference's loop: survivors carry over, detection on
+    key-frames only, src/tracking.cpp:69-70, :168-177, :254) against the CPU pipeline: tracks, key-frame flags and survivor
+    indices per sequence and frame, bit-exact."""
+    from oracle.cpu_pipeline import CpuFrontend
+    from svo_b200.frontend import make_params
+    w, h, S, T, max_tracks, ftt = 320, 240, 3, 7, 400, 400
+    seqs = np.stack([synth.sequence(w, h, seed, T, times=[v * t for t in range(T)]) for seed, v in ((5, 3.0), (6, 0.1), (7, 1.5))])
+    fin, fout = tmp_path / "bin.bin", tmp_path / "bout.bin"
+    with open(fin, "wb") as f:
+        np.array([w, h, S, T, max_tracks], np.int32).tofile(f)
+        np.ascontiguousarray(seqs.transpose(1, 0, 2, 3)).tofile(f)
+    r = subprocess.run([exe, "--batch", str(fin), str(fout), str(ftt)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    buf = open(fout, "rb").read()
+    off = 0
+
+    def take(dtype, n):
+        nonlocal off
+        out = np.frombuffer(buf, dtype, n, off)
+        off += out.nbytes
+        return out
+
+    _, pdict = make_params(w, h, max_tracks=max_tracks, mask_half=10.0, carry_tracks=1, features_to_track=ftt)
+    cpus = [CpuFrontend(pdict, impl="orc") for _ in range(S)]
+    kfs = []
+    for t in range(T):
+        for s in range(S):
+            ref = cpus[s].step(seqs[s, t])
+            nt = int(take(np.int32, 1)[0])
+            xy, st, er = take(np.float32, 2 * nt).reshape(nt, 2), take(np.uint8, nt), take(np.float32, nt)
+            nb = int(take(np.int32, 1)[0])
+            feats = take(np.float32, 2 * nb).reshape(nb, 2)
+            nk = int(take(np.int32, 1)[0])
+            kf = int(take(np.int32, 1)[0])
+            ns = int(take(np.int32, 1)[0])
+            surv = take(np.int32, ns)
+            assert nt == len(ref["next_xy"]) and np.array_equal(xy, ref["next_xy"]) and np.array_equal(st, ref["status"]), (t, s)
+            assert np.array_equal(er, ref["err"]) and kf == ref["keyframe"] and nk == len(ref["kp_xy"]), (t, s)
+            assert np.array_equal(feats, ref["bucket_xy"]) and np.array_equal(surv, ref.get("survivor_index", np.zeros(0, np.int32))), (t, s)
+            kfs.append(kf)
+    assert any(k == 0 for k in kfs[S:]) and any(k == 1 for k in kfs[S:])
