@@ -265,7 +265,7 @@ typedef struct svo_gpu_step_outputs {
 
 /* One frame of `batch` independent streams: ingest images[b] (host or device memory), build its pyramid, run LK from
  * each lane's previous frame on that lane's current tracks, run FAST (+ tracked-points mask) on the new frame, bucket
- * the detections, and make the first max_tracks of them the lane's tracks for the next call.  The context ping-pongs
+ * the detections, and make the first max_tracks of them the lane's tracks for the next call.  The context cycles through
  * a ring of three slots internally (SVO_GPU_NUM_SLOTS-3 .. -1: this frame, the previous one, and a free
  * one for the next frame's copy and pyramid build).  Lanes never interact; this is how independent sequences share one
  * GPU (and, with one context per device, several GPUs). */
