@@ -27,6 +27,9 @@ constexpr int RW = TW + 8, RH = TH + 8;   // staged image region (halo 3 for the
 constexpr int RWW = RW / 4;               // words per staged row
 constexpr int SH = TH + 2;   // score region, origin (x0-1, y0-1) = staged (3, 3)
 constexpr int NG = RWW;                   // 4-pixel groups per score row (staged columns 4g .. 4g+3)
+constexpr int MX = 32, MY = 2;            // margin of the tile's mask bit plane (columns, rows)
+constexpr int MW = TW / 32 + 2, MH = TH + 2 * MY;   // its size in words per row and rows
+static_assert(SH * NG < 65536 && TW % 32 == 0, "group indices are stored as 16 bits");
 
 // ---- packed arithmetic: two pixels per 32-bit register (16-bit fields); a 4-pixel group = an "even" register (pixels
 // 0, 2) and an "odd" one (pixels 1, 3).  sm_100a has 3-input packed min/max (VIMNMX3.U16x2), which ptxas forms from
@@ -94,8 +97,11 @@ __global__ void __launch_bounds__(NT) fast_tile_kernel(const uint8_t* __restrict
     __shared__ __align__(16) uint32_t simg_pad[RH * RWW + 2];   // one pad word on each side: ring_word reads words g-1, g+1
     __shared__ __align__(16) uint32_t sbest_pad[SH * RWW + 2];  // excess of the score over the threshold, one byte per pixel,
                                                                 // same column layout as the staged image (0 = no corner)
-    // mask given as points (src/tracking.cpp:76-79): bit x of word (row, x / 32) = mask pixel of tile pixel (x, row) != 0
-    __shared__ uint32_t smask[TH * (TW / 32)];
+    // mask given as points (src/tracking.cpp:76-79), as a bit plane over the tile and a margin of 32 columns / 2 rows around
+    // it: bit (x - (x0 - 32), y - (y0 - 2)) = mask pixel (x, y) != 0.  Bits outside the frame stay set.
+    __shared__ uint32_t smask[MH * MW];
+    __shared__ uint16_t slist[SH * NG];   // the 4-pixel groups of the score region that need a score (see below)
+    __shared__ int scount;
     uint32_t* simg = simg_pad + 1;
     uint32_t* sbest = sbest_pad + 1;
     const int tid = threadIdx.x;
@@ -104,8 +110,10 @@ __global__ void __launch_bounds__(NT) fast_tile_kernel(const uint8_t* __restrict
     const uint8_t* src = raw + (size_t)lane_id * raw_lane;
 
     if (tid == 0) { simg_pad[0] = 0; simg_pad[RH * RWW + 1] = 0; sbest_pad[0] = 0; sbest_pad[SH * RWW + 1] = 0; }
-    if (mp.pts)
-        for (int i = tid; i < TH * (TW / 32); i += NT) smask[i] = 0xffffffffu;
+    if (mp.pts) {
+        for (int i = tid; i < MH * MW; i += NT) smask[i] = 0xffffffffu;
+        if (tid == 0) scount = 0;
+    }
 
     // ---- stage the (TW+8) x (TH+8) region; coordinates are clamped to the image (clamped pixels are never used by a
     //      valid candidate: those sit at least 3 px inside the image)
@@ -138,17 +146,52 @@ __global__ void __launch_bounds__(NT) fast_tile_kernel(const uint8_t* __restrict
         const float2* pts = mp.pts + (size_t)lane_id * mp.pts_lane;
         for (int i = tid; i < n; i += NT) {
             const float2 p = __ldg(pts + i);
-            // clamped to the tile before the tile origin is subtracted (the conversions saturate at INT_MIN / INT_MAX)
-            const int ya = max(__float2int_rn(__fsub_rn(p.y, mp.half)), y0) - y0, yb = min(__float2int_rn(__fadd_rn(p.y, mp.half)), y0 + TH - 1) - y0;
+            // clamped to the plane before its origin is subtracted (the conversions saturate at INT_MIN / INT_MAX)
+            const int my0 = y0 - MY, mx0 = x0 - MX;
+            const int ya = max(__float2int_rn(__fsub_rn(p.y, mp.half)), my0) - my0, yb = min(__float2int_rn(__fadd_rn(p.y, mp.half)), my0 + MH - 1) - my0;
             if (ya > yb) continue;
-            const int xa = max(__float2int_rn(__fsub_rn(p.x, mp.half)), x0) - x0, xb = min(__float2int_rn(__fadd_rn(p.x, mp.half)), x0 + TW - 1) - x0;
+            const int xa = max(__float2int_rn(__fsub_rn(p.x, mp.half)), mx0) - mx0, xb = min(__float2int_rn(__fadd_rn(p.x, mp.half)), mx0 + 32 * MW - 1) - mx0;
             if (xa > xb) continue;
             for (int wd = xa >> 5; wd <= xb >> 5; ++wd) {
                 const int lo = max(xa - 32 * wd, 0), hi = min(xb - 32 * wd, 31);
                 const uint32_t clr = ~((0xffffffffu >> (31 - hi)) & (0xffffffffu << lo));
-                for (int y = ya; y <= yb; ++y) atomicAnd(&smask[y * (TW / 32) + wd], clr);
+                for (int y = ya; y <= yb; ++y) atomicAnd(&smask[y * MW + wd], clr);
             }
         }
+    }
+
+    // ---- which groups need a score at all.  The reference masks two thirds of the frame (2 000 boxes of 21 x 21 px), and a
+    //      pixel's score can only reach the output as its own response (if it survives the mask) or through the NMS of one of
+    //      its 8 neighbours (if THAT one survives the mask): a pixel that is masked together with all its neighbours needs no
+    //      score.  A group of four such pixels (its 6 x 3 neighbourhood fully masked: ~60 % of the groups on the bench frames)
+    //      gets 0 and the rest are compacted into a list, so that the warps of pass 1 stay full.
+    const bool use_list = mp.pts != nullptr;
+    int ngroups = SH * NG;
+    if (use_list) {
+        __syncthreads();   // the bit plane is complete
+        const uint32_t lt_ = (1u << (tid & 31)) - 1u;
+        for (int base = 0; base < SH * NG; base += NT) {
+            const int idx = base + tid;
+            bool work = false;
+            if (idx < SH * NG) {
+                const int r = idx / NG, g = idx - r * NG;
+                // score row r = image row y0 - 1 + r -> plane rows r .. r + 2; group g = image columns x0 - 4 + 4 g .. + 3,
+                // neighbourhood from x0 - 5 + 4 g -> plane bit 4 g + MX - 5, six bits
+                const int bx = 4 * g + MX - 5;
+                const uint32_t* m0 = smask + r * MW + (bx >> 5);
+                const uint32_t bits = __funnelshift_r(m0[0], m0[1], bx & 31) | __funnelshift_r(m0[MW], m0[MW + 1], bx & 31) |
+                                      __funnelshift_r(m0[2 * MW], m0[2 * MW + 1], bx & 31);
+                work = (bits & 0x3fu) != 0;
+                if (!work) sbest[r * RWW + g] = 0;
+            }
+            const unsigned m = __ballot_sync(0xffffffffu, work);
+            int wbase = 0;
+            if ((tid & 31) == 0 && m) wbase = atomicAdd(&scount, __popc(m));
+            wbase = __shfl_sync(0xffffffffu, wbase, 0);
+            if (work) slist[wbase + __popc(m & lt_)] = (uint16_t)idx;
+        }
+        __syncthreads();
+        ngroups = scount;
     }
 
     // ---- pass 1: dense packed corner score of every 4-pixel group of the score region (rows y0-1 .. y0+TH, staged
@@ -157,7 +200,8 @@ __global__ void __launch_bounds__(NT) fast_tile_kernel(const uint8_t* __restrict
     const bool edge_tile = x0 - 4 < 3 || x0 + TW + 3 > w - 4 || y0 - 1 < 3 || y0 + TH > h - 4;
     const uint32_t bias = 0x01000100u;
     const uint32_t tt = (uint32_t)t * 0x00010001u;
-    for (int idx = tid; idx < SH * NG; idx += NT) {
+    for (int it = tid; it < ngroups; it += NT) {
+        const int idx = use_list ? (int)slist[it] : it;
         const int r = idx / NG, g = idx - r * NG;
         const uint32_t* c = simg + (r + 3) * RWW + g;   // centre row of score row r
         const uint32_t wc = c[0];
@@ -235,7 +279,7 @@ __global__ void __launch_bounds__(NT) fast_tile_kernel(const uint8_t* __restrict
             // keep <=> s > m <=> (s + 0x7fff) - m has bit 15 set (fields stay inside [0x7f00, 0x80fe])
             const uint32_t ke = (even_px(wc) + 0x7fff7fffu) - me, ko = (odd_px(wc) + 0x7fff7fffu) - mo;
             bits = ((ke >> 15) & 1u) | ((ko >> 14) & 2u) | ((ke >> 29) & 4u) | ((ko >> 28) & 8u);
-            if (bits && mp.pts) bits &= smask[r * (TW / 32) + (ln >> 3)] >> (4 * (ln & 7));
+            if (bits && mp.pts) bits &= smask[(r + MY) * MW + MX / 32 + (ln >> 3)] >> (4 * (ln & 7));
             if (bits && mask) {
                 const uint8_t* mrow = mask + (size_t)lane_id * mask_lane + (size_t)gy * mask_pitch + x0 + 4 * ln;
 #pragma unroll
