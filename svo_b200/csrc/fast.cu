@@ -144,8 +144,13 @@ __global__ void __launch_bounds__(NT) fast_tile_kernel(const uint8_t* __restrict
     if (mp.pts) {
         const int n = min(mp.n_dev[lane_id], mp.n_max);
         const float2* pts = mp.pts + (size_t)lane_id * mp.pts_lane;
+        // most points are nowhere near this tile: one float comparison per axis (with a pixel of slack for the rounding below)
+        // turns them away before any float -> int conversion (quarter-rate pipe); NaN coordinates fall through to the exact test
+        const float cy = (float)(y0 - MY) + 0.5f * (float)(MH - 1), ry = fabsf(mp.half) + 0.5f * (float)(MH - 1) + 1.f;
+        const float cx = (float)(x0 - MX) + 0.5f * (float)(32 * MW - 1), rx = fabsf(mp.half) + 0.5f * (float)(32 * MW - 1) + 1.f;
         for (int i = tid; i < n; i += NT) {
             const float2 p = __ldg(pts + i);
+            if (fabsf(p.y - cy) > ry || fabsf(p.x - cx) > rx) continue;
             // clamped to the plane before its origin is subtracted (the conversions saturate at INT_MIN / INT_MAX)
             const int my0 = y0 - MY, mx0 = x0 - MX;
             const int ya = max(__float2int_rn(__fsub_rn(p.y, mp.half)), my0) - my0, yb = min(__float2int_rn(__fadd_rn(p.y, mp.half)), my0 + MH - 1) - my0;
@@ -170,11 +175,12 @@ __global__ void __launch_bounds__(NT) fast_tile_kernel(const uint8_t* __restrict
     if (use_list) {
         __syncthreads();   // the bit plane is complete
         const uint32_t lt_ = (1u << (tid & 31)) - 1u;
-        for (int base = 0; base < SH * NG; base += NT) {
+        int r = tid / NG, g = tid - r * NG;   // (row, group) of idx, advanced without divisions
+        for (int base = 0; base < SH * NG; base += NT, r += NT / NG, g += NT % NG) {
             const int idx = base + tid;
+            if (g >= NG) { g -= NG; ++r; }
             bool work = false;
             if (idx < SH * NG) {
-                const int r = idx / NG, g = idx - r * NG;
                 // score row r = image row y0 - 1 + r -> plane rows r .. r + 2; group g = image columns x0 - 4 + 4 g .. + 3,
                 // neighbourhood from x0 - 5 + 4 g -> plane bit 4 g + MX - 5, six bits
                 const int bx = 4 * g + MX - 5;
