@@ -117,23 +117,35 @@ __global__ void __launch_bounds__(NT) fast_tile_kernel(const uint8_t* __restrict
 
     // ---- stage the (TW+8) x (TH+8) region; coordinates are clamped to the image (clamped pixels are never used by a
     //      valid candidate: those sit at least 3 px inside the image)
-    for (int i = tid; i < RH * RWW; i += NT) {
-        const int r = i / RWW, cw = i - r * RWW;
-        const int gy = min(max(y0 - 4 + r, 0), h - 1);
-        const int gx = x0 - 4 + cw * 4;
-        const uint8_t* row = src + (size_t)gy * raw_pitch;
-        uint32_t v;
-        if (gx >= 4 && gx + 7 < w) {
-            // two aligned words + funnel shift: any row pitch / alignment; the eight bytes read lie inside this row
-            const uintptr_t addr = reinterpret_cast<uintptr_t>(row + gx);
-            const uint32_t* wp = reinterpret_cast<const uint32_t*>(addr & ~(uintptr_t)3);
-            v = __funnelshift_r(__ldg(wp), __ldg(wp + 1), 8 * (int)(addr & 3));
-        } else {
-            v = 0;
+    //      Four words per thread and round, every load of the round issued before the first use (the kernel's first phase is
+    //      all latency: one CTA has nothing else to run).  Words at the frame border (rare) are assembled byte by byte.
+    constexpr int SU = 4;
+    for (int i0 = tid; i0 < RH * RWW; i0 += SU * NT) {
+        uint32_t lo[SU], hi[SU];
+        int sh[SU];
 #pragma unroll
-            for (int b = 0; b < 4; ++b) v |= (uint32_t)__ldg(row + min(max(gx + b, 0), w - 1)) << (8 * b);
+        for (int k = 0; k < SU; ++k) {
+            const int i = min(i0 + k * NT, RH * RWW - 1);
+            const int r = i / RWW, cw = i - r * RWW;
+            const int gy = min(max(y0 - 4 + r, 0), h - 1);
+            const int gx = x0 - 4 + cw * 4;
+            const uint8_t* row = src + (size_t)gy * raw_pitch;
+            if (gx >= 4 && gx + 7 < w) {
+                // two aligned words + funnel shift: any row pitch / alignment; the eight bytes read lie inside this row
+                const uintptr_t addr = reinterpret_cast<uintptr_t>(row + gx);
+                const uint32_t* wp = reinterpret_cast<const uint32_t*>(addr & ~(uintptr_t)3);
+                lo[k] = __ldg(wp); hi[k] = __ldg(wp + 1);
+                sh[k] = 8 * (int)(addr & 3);
+            } else {
+                uint32_t v = 0;
+#pragma unroll
+                for (int b = 0; b < 4; ++b) v |= (uint32_t)__ldg(row + min(max(gx + b, 0), w - 1)) << (8 * b);
+                lo[k] = v; hi[k] = 0; sh[k] = 0;
+            }
         }
-        simg[i] = v;
+#pragma unroll
+        for (int k = 0; k < SU; ++k)
+            if (i0 + k * NT < RH * RWW) simg[i0 + k * NT] = __funnelshift_r(lo[k], hi[k], sh[k]);
     }
     __syncthreads();
 
@@ -148,8 +160,15 @@ __global__ void __launch_bounds__(NT) fast_tile_kernel(const uint8_t* __restrict
         // turns them away before any float -> int conversion (quarter-rate pipe); NaN coordinates fall through to the exact test
         const float cy = (float)(y0 - MY) + 0.5f * (float)(MH - 1), ry = fabsf(mp.half) + 0.5f * (float)(MH - 1) + 1.f;
         const float cx = (float)(x0 - MX) + 0.5f * (float)(32 * MW - 1), rx = fabsf(mp.half) + 0.5f * (float)(32 * MW - 1) + 1.f;
-        for (int i = tid; i < n; i += NT) {
-            const float2 p = __ldg(pts + i);
+        constexpr int PU = 8;   // points per thread and round, all loaded before the first is looked at
+        for (int i0 = tid; i0 < n; i0 += PU * NT) {
+          float2 pk[PU];
+#pragma unroll
+          for (int k = 0; k < PU; ++k) pk[k] = __ldg(pts + min(i0 + k * NT, n - 1));
+#pragma unroll
+          for (int k = 0; k < PU; ++k) {
+            if (i0 + k * NT >= n) break;
+            const float2 p = pk[k];
             if (fabsf(p.y - cy) > ry || fabsf(p.x - cx) > rx) continue;
             // clamped to the plane before its origin is subtracted (the conversions saturate at INT_MIN / INT_MAX)
             const int my0 = y0 - MY, mx0 = x0 - MX;
@@ -162,6 +181,7 @@ __global__ void __launch_bounds__(NT) fast_tile_kernel(const uint8_t* __restrict
                 const uint32_t clr = ~((0xffffffffu >> (31 - hi)) & (0xffffffffu << lo));
                 for (int y = ya; y <= yb; ++y) atomicAnd(&smask[y * MW + wd], clr);
             }
+          }
         }
     }
 
