@@ -88,7 +88,7 @@ __device__ __forceinline__ uint32_t packed_best(const uint32_t (&D)[16])
 
 // NT threads per CTA: 128 (8 192 registers per CTA, eight CTAs per SM) or 256
 template <int NT>
-__global__ void __launch_bounds__(NT) fast_tile_kernel(const uint8_t* __restrict__ raw, size_t raw_pitch, size_t raw_lane,
+__global__ void __launch_bounds__(NT, NT == 128 ? 8 : 1) fast_tile_kernel(const uint8_t* __restrict__ raw, size_t raw_pitch, size_t raw_lane,
                                                        int w, int h, int t, int nms, const uint8_t* __restrict__ mask,
                                                        size_t mask_pitch, size_t mask_lane, FastBufs fb, int ntx,
                                                        FastMaskPts mp)
