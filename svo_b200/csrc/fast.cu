@@ -101,6 +101,7 @@ __global__ void __launch_bounds__(NT, NT == 128 ? 8 : 1) fast_tile_kernel(const 
     // it: bit (x - (x0 - 32), y - (y0 - 2)) = mask pixel (x, y) != 0.  Bits outside the frame stay set.
     __shared__ uint32_t smask[MH * MW];
     __shared__ uint16_t slist[SH * NG];   // the 4-pixel groups of the score region that need a score (see below)
+    __shared__ int scount;
     uint32_t* simg = simg_pad + 1;
     uint32_t* sbest = sbest_pad + 1;
     const int tid = threadIdx.x;
@@ -111,6 +112,7 @@ __global__ void __launch_bounds__(NT, NT == 128 ? 8 : 1) fast_tile_kernel(const 
     if (tid == 0) { simg_pad[0] = 0; simg_pad[RH * RWW + 1] = 0; sbest_pad[0] = 0; sbest_pad[SH * RWW + 1] = 0; }
     if (mp.pts) {
         for (int i = tid; i < MH * MW; i += NT) smask[i] = 0xffffffffu;
+        if (tid == 0) scount = 0;
     }
 
     // ---- stage the (TW+8) x (TH+8) region; coordinates are clamped to the image (clamped pixels are never used by a
@@ -165,28 +167,19 @@ __global__ void __launch_bounds__(NT, NT == 128 ? 8 : 1) fast_tile_kernel(const 
           for (int k = 0; k < PU; ++k) pk[k] = __ldg(pts + min(i0 + k * NT, n - 1));
 #pragma unroll
           for (int k = 0; k < PU; ++k) {
-            if (i0 - tid + k * NT >= n) break;   // warp-uniform (i0 - tid is the round's first point): the whole warp votes below
+            if (i0 + k * NT >= n) break;
             const float2 p = pk[k];
-            // exact box, clamped to the plane before its origin is subtracted (the conversions saturate at INT_MIN / INT_MAX)
+            if (fabsf(p.y - cy) > ry || fabsf(p.x - cx) > rx) continue;
+            // clamped to the plane before its origin is subtracted (the conversions saturate at INT_MIN / INT_MAX)
             const int my0 = y0 - MY, mx0 = x0 - MX;
-            int ya = 1, yb = 0, xa = 1, xb = 0;
-            if (i0 + k * NT < n && !(fabsf(p.y - cy) > ry || fabsf(p.x - cx) > rx)) {
-                ya = max(__float2int_rn(__fsub_rn(p.y, mp.half)), my0) - my0; yb = min(__float2int_rn(__fadd_rn(p.y, mp.half)), my0 + MH - 1) - my0;
-                xa = max(__float2int_rn(__fsub_rn(p.x, mp.half)), mx0) - mx0; xb = min(__float2int_rn(__fadd_rn(p.x, mp.half)), mx0 + 32 * MW - 1) - mx0;
-            }
-            // few lanes hold a box that reaches the plane (about 2 % of the points do): the warp clears them one by one, a lane
-            // per row, instead of letting each holder walk its rows while 31 lanes wait
-            unsigned hits = __ballot_sync(0xffffffffu, ya <= yb && xa <= xb);
-            while (hits) {
-                const int srcl = __ffs((int)hits) - 1;
-                hits &= hits - 1u;
-                const int bya = __shfl_sync(0xffffffffu, ya, srcl), byb = __shfl_sync(0xffffffffu, yb, srcl);
-                const int bxa = __shfl_sync(0xffffffffu, xa, srcl), bxb = __shfl_sync(0xffffffffu, xb, srcl);
-                for (int y = bya + (tid & 31); y <= byb; y += 32)
-                    for (int wd = bxa >> 5; wd <= bxb >> 5; ++wd) {
-                        const int lo = max(bxa - 32 * wd, 0), hi = min(bxb - 32 * wd, 31);
-                        atomicAnd(&smask[y * MW + wd], ~((0xffffffffu >> (31 - hi)) & (0xffffffffu << lo)));
-                    }
+            const int ya = max(__float2int_rn(__fsub_rn(p.y, mp.half)), my0) - my0, yb = min(__float2int_rn(__fadd_rn(p.y, mp.half)), my0 + MH - 1) - my0;
+            if (ya > yb) continue;
+            const int xa = max(__float2int_rn(__fsub_rn(p.x, mp.half)), mx0) - mx0, xb = min(__float2int_rn(__fadd_rn(p.x, mp.half)), mx0 + 32 * MW - 1) - mx0;
+            if (xa > xb) continue;
+            for (int wd = xa >> 5; wd <= xb >> 5; ++wd) {
+                const int lo = max(xa - 32 * wd, 0), hi = min(xb - 32 * wd, 31);
+                const uint32_t clr = ~((0xffffffffu >> (31 - hi)) & (0xffffffffu << lo));
+                for (int y = ya; y <= yb; ++y) atomicAnd(&smask[y * MW + wd], clr);
             }
           }
         }
@@ -197,21 +190,17 @@ __global__ void __launch_bounds__(NT, NT == 128 ? 8 : 1) fast_tile_kernel(const 
     //      its 8 neighbours (if THAT one survives the mask): a pixel that is masked together with all its neighbours needs no
     //      score.  A group of four such pixels (its 6 x 3 neighbourhood fully masked: ~60 % of the groups on the bench frames)
     //      gets 0 and the rest are compacted into a list, so that the warps of pass 1 stay full.
-    //      Each warp compacts its own contiguous share of the groups into its own stretch of the list and then scores exactly
-    //      those: no atomics, and no barrier between the two loops.
     const bool use_list = mp.pts != nullptr;
-    constexpr int NW = NT / 32, CH = (SH * NG + NW - 1) / NW;   // groups per warp
-    const int wfirst = (tid >> 5) * CH, wend = min(wfirst + CH, SH * NG);
-    int ngroups = wend - wfirst;
+    int ngroups = SH * NG;
     if (use_list) {
         __syncthreads();   // the bit plane is complete
         const uint32_t lt_ = (1u << (tid & 31)) - 1u;
-        int cnt = 0;
-        int r = (wfirst + (tid & 31)) / NG, g = wfirst + (tid & 31) - r * NG;   // (row, group) of idx, advanced without divisions
-        for (int idx = wfirst + (tid & 31); idx - (tid & 31) < wend; idx += 32, g += 32) {
+        int r = tid / NG, g = tid - r * NG;   // (row, group) of idx, advanced without divisions
+        for (int base = 0; base < SH * NG; base += NT, r += NT / NG, g += NT % NG) {
+            const int idx = base + tid;
             if (g >= NG) { g -= NG; ++r; }
             bool work = false;
-            if (idx < wend) {
+            if (idx < SH * NG) {
                 // score row r = image row y0 - 1 + r -> plane rows r .. r + 2; group g = image columns x0 - 4 + 4 g .. + 3,
                 // neighbourhood from x0 - 5 + 4 g -> plane bit 4 g + MX - 5, six bits
                 const int bx = 4 * g + MX - 5;
@@ -222,21 +211,23 @@ __global__ void __launch_bounds__(NT, NT == 128 ? 8 : 1) fast_tile_kernel(const 
                 if (!work) sbest[r * RWW + g] = 0;
             }
             const unsigned m = __ballot_sync(0xffffffffu, work);
-            if (work) slist[wfirst + cnt + __popc(m & lt_)] = (uint16_t)idx;
-            cnt += __popc(m);
+            int wbase = 0;
+            if ((tid & 31) == 0 && m) wbase = atomicAdd(&scount, __popc(m));
+            wbase = __shfl_sync(0xffffffffu, wbase, 0);
+            if (work) slist[wbase + __popc(m & lt_)] = (uint16_t)idx;
         }
-        __syncwarp();
-        ngroups = cnt;
+        __syncthreads();
+        ngroups = scount;
     }
 
-    // ---- pass 1: packed corner score of the listed 4-pixel groups of the score region (rows y0-1 .. y0+TH, staged
+    // ---- pass 1: dense packed corner score of every 4-pixel group of the score region (rows y0-1 .. y0+TH, staged
     //      columns 0 .. RW-1): sbest byte = max(best - t, 0), where best = cornerScore + 1.
     // does the score region (x0-4 .. x0+TW+3, y0-1 .. y0+TH) reach into the 3-px frame?  (CTA-uniform)
     const bool edge_tile = x0 - 4 < 3 || x0 + TW + 3 > w - 4 || y0 - 1 < 3 || y0 + TH > h - 4;
     const uint32_t bias = 0x01000100u;
     const uint32_t tt = (uint32_t)t * 0x00010001u;
-    for (int it = tid & 31; it < ngroups; it += 32) {
-        const int idx = use_list ? (int)slist[wfirst + it] : wfirst + it;
+    for (int it = tid; it < ngroups; it += NT) {
+        const int idx = use_list ? (int)slist[it] : it;
         const int r = idx / NG, g = idx - r * NG;
         const uint32_t* c = simg + (r + 3) * RWW + g;   // centre row of score row r
         const uint32_t wc = c[0];
