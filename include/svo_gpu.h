@@ -149,6 +149,41 @@ SVO_GPU_API int svo_gpu_fast_masked_by_points(svo_gpu_ctx* ctx, int slot, int th
 SVO_GPU_API int svo_gpu_bucket(svo_gpu_ctx* ctx, float* xy_inout, int* ages_inout, int n_in, int img_w, int img_h,
                                int bucket_size, int per_bucket, int capacity, int* n_out);
 
+/* Bucketing without any allocation.  No counterpart in the reference (which has no device code); same rule and same result
+ * as svo_gpu_bucket, for callers that cannot obtain device memory themselves or through a context:
+ *   - a per-frame tracking thread with a latency budget: cudaMalloc / cudaFree take driver-wide locks and can wait for every
+ *     stream of the device, so such loops are written to allocate nothing once they run -- svo_gpu_create allocates all of a
+ *     context's buffers, and svo_gpu_bucket re-allocates its bucket tables when a call needs a finer grid than any before;
+ *   - a plug-in inside an application that has handed all of the GPU's memory to its own pool (an inference server, a
+ *     simulator): a cudaMalloc from a guest library fails there, and the plug-in only ever sees buffers it is given.
+ * Such a caller passes device buffers it already owns and needs no svo_gpu_ctx.  The per-bucket tables (arrival count,
+ * largest index and the per_bucket smallest indices of each bucket -- the scratch svo_gpu_bucket keeps in context buffers)
+ * live in ONE static device array of SVO_GPU_BUCKET_STATIC_BYTES that is part of the library image: every GPU on which this
+ * library's kernels get loaded holds it until the process exits, whether or not this function is ever called.
+ *   limit      ((img_h / bucket_size + 1) * (img_w / bucket_size + 1)) * (2 + per_bucket) * 4 + 256 bytes must fit the array
+ *              (the reference's 1241x376 frame with 32-px buckets of 5 needs 13 KB; 3840x2160 with 16-px buckets of 5 needs
+ *              0.9 MB); anything larger returns SVO_GPU_E_CAPACITY and says so -- nothing is truncated.  n_in is not limited.
+ *   inputs     xy_in_dev [n_in][2] floats and ages_in_dev_or_null [n_in] (NULL = all ages 0, FeatureSet::appendNewFeatures)
+ *              in DEVICE memory; not modified.
+ *   outputs    xy_out_dev [capacity][2], ages_out_dev [capacity] in DEVICE memory, not overlapping the inputs; *n_out (host)
+ *              = bucketed features.  More than `capacity` of them: SVO_GPU_E_CAPACITY, *n_out = the count required, the
+ *              first `capacity` entries written.  xy arrays must be 8-byte aligned.
+ *   stream     a cudaStream_t (as void*) of the CURRENT device, or NULL for the default stream.  The work is enqueued there,
+ *              after whatever the caller enqueued to produce the inputs; the call returns when it is done (outputs valid).
+ *   errors     codes as everywhere in this header; the message goes to errbuf_or_null (errbuf_len bytes, NUL-terminated).
+ *   first call The first call on each device looks up where the static array lives on that device (the device that is
+ *              current at that moment), which may make the CUDA runtime load this library's kernels there.  Make that first
+ *              call during start-up, before any stream capture begins on the device; later calls only launch work.
+ *   sharing    All calls in the process use the same array on a given device, and the array keeps the previous call's
+ *              tables: each call clears the part it is about to use before reading it.  Two calls whose GPU work can overlap
+ *              (two host threads, or two streams, on one device) would corrupt each other's tables: serialise them.
+ * The function calls no cudaMalloc / cudaFree / cudaHostAlloc and no library routine that does; its only transfers are a
+ * 4-byte memset and one 8-byte read-back (count and error flag) into a local variable. */
+#define SVO_GPU_BUCKET_STATIC_BYTES (1 << 20)
+SVO_GPU_API int svo_gpu_bucket_static(const float* xy_in_dev, const int* ages_in_dev_or_null, int n_in, int img_w, int img_h,
+                                      int bucket_size, int per_bucket, float* xy_out_dev, int* ages_out_dev, int capacity,
+                                      int* n_out, void* stream, char* errbuf_or_null, size_t errbuf_len);
+
 /* ---------------------------------------------------------------------------------------------- KLT ----------- */
 
 /* cv::calcOpticalFlowPyrLK(prevImg, nextImg, prevPts, nextPts, status, err, winSize, maxLevel, criteria, flags,

@@ -51,6 +51,8 @@ SYMBOLS = {
                                                 C.c_void_p, C.c_void_p, C.c_int, _i32p]),
     "svo_gpu_bucket": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                  C.c_int, _i32p]),
+    "svo_gpu_bucket_static": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                        C.c_void_p, C.c_int, _i32p, C.c_void_p, C.c_char_p, C.c_size_t]),
     "svo_gpu_klt": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
                               C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, C.c_double]),
     "svo_gpu_last_klt_iterations": (C.c_longlong, [C.c_void_p]),
@@ -127,6 +129,21 @@ def load():
 
 def _ptr(a):
     return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def bucket_static(xy_in_ptr, ages_in_ptr, n_in, img_w, img_h, bucket_size, per_bucket, xy_out_ptr, ages_out_ptr, capacity,
+                  stream=0):
+    """svo_gpu_bucket_static: bucketing on caller-owned DEVICE buffers (raw addresses) with the tables in the library's static
+    device array -- no context and no allocation.  Returns the number of bucketed features written to the output buffers."""
+    m = C.c_int(0)
+    msg = C.create_string_buffer(512)
+    rc = load().svo_gpu_bucket_static(xy_in_ptr, ages_in_ptr, n_in, img_w, img_h, bucket_size, per_bucket, xy_out_ptr,
+                                      ages_out_ptr, capacity, C.byref(m), stream, msg, len(msg))
+    if rc != OK:
+        e = SvoGpuError(rc, msg.value.decode("utf-8", "replace"))
+        e.required = m.value
+        raise e
+    return m.value
 
 
 class Context:

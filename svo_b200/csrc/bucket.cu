@@ -17,6 +17,8 @@
 //   emit kernel: each CTA owns 256 consecutive entries of the emission sequence, recomputes the offset of its first
 //   entry by summing min(m, k) over all earlier entries (a few thousand L2 reads), scans its own, and gathers.
 #include <limits.h>
+#include <stdarg.h>
+#include <stdio.h>
 
 #include <algorithm>
 
@@ -285,3 +287,131 @@ void launch_bucket(cudaStream_t st, const float2* in_xy, const int* in_age, size
 }
 
 }  // namespace svo
+
+// ================================================================================================ svo_gpu_bucket_static
+// Bucketing for callers that are not allowed to allocate (include/svo_gpu.h has the user-facing contract).  It runs the very
+// same clear / insert / emit kernels as launch_bucket's global-memory path; the only difference is where the per-bucket
+// tables live: not in cudaMalloc'ed context buffers but in the file-scope device array below, which the CUDA module reserves
+// once for every device that loads this library and never gives back.
+namespace svo {
+namespace {
+
+constexpr int kStaticInts = SVO_GPU_BUCKET_STATIC_BYTES / (int)sizeof(int);
+constexpr int kStaticHead = 64;   // ints [0] output length, [1] error flag, [2] "no limit" list length; tables start at 256 B
+constexpr int kStaticMaxDevices = 64;
+
+__device__ __align__(256) int g_bucket_static[kStaticInts];
+
+// `g_bucket_static` above is what DEVICE code calls the array.  In host code that name is only the runtime's handle of the
+// symbol; the address a kernel can dereference has to be asked for, once per device and with that device current.
+std::atomic<int*> g_bucket_static_dev[kStaticMaxDevices];
+
+int static_fail(char* buf, size_t len, int code, const char* fmt, ...)
+{
+    if (buf && len) {
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(buf, len, fmt, ap);
+        va_end(ap);
+    }
+    return code;
+}
+
+bool on_device(const void* p)
+{
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
+}
+
+}  // namespace
+}  // namespace svo
+
+extern "C" int svo_gpu_bucket_static(const float* xy_in_dev, const int* ages_in_dev_or_null, int n_in, int img_w, int img_h,
+                                     int bucket_size, int per_bucket, float* xy_out_dev, int* ages_out_dev, int capacity,
+                                     int* n_out, void* stream, char* errbuf_or_null, size_t errbuf_len)
+{
+    using namespace svo;
+    char* eb = errbuf_or_null;
+    const size_t el = errbuf_len;
+    if (eb && el) eb[0] = 0;
+    // ---- the same argument rules as svo_gpu_bucket
+    if (!n_out || n_in < 0 || capacity < 0 || (n_in > 0 && !xy_in_dev) || (capacity > 0 && (!xy_out_dev || !ages_out_dev)))
+        return static_fail(eb, el, SVO_GPU_E_ARG, "svo_gpu_bucket_static: null pointer or negative count");
+    if (bucket_size < 1 || img_w < 0 || img_h < 0)
+        return static_fail(eb, el, SVO_GPU_E_ARG, "bucket_size %d / image %dx%d invalid", bucket_size, img_w, img_h);
+    if (per_bucket < 1 && n_in > 0) return static_fail(eb, el, SVO_GPU_E_ARG, "features_per_bucket %d < 1", per_bucket);
+    if (per_bucket < 1) per_bucket = 1;
+    if (((uintptr_t)xy_in_dev | (uintptr_t)xy_out_dev) & 7u)
+        return static_fail(eb, el, SVO_GPU_E_ARG, "xy_in_dev / xy_out_dev must be 8-byte aligned (they are read and written as x,y pairs)");
+    // ---- the limit of this entry point: the bucket tables have to fit the static array
+    const long long Hc = img_h / bucket_size, Wc = img_w / bucket_size;
+    const long long nb = (Hc + 1) * (Wc + 1);
+    const long long need = kStaticHead + nb * (2 + (long long)per_bucket);
+    if (need > kStaticInts)
+        return static_fail(eb, el, SVO_GPU_E_CAPACITY,
+                           "svo_gpu_bucket_static: %lld buckets x (2 + %d per bucket) need %lld bytes of table, the static scratch "
+                           "array holds %d (SVO_GPU_BUCKET_STATIC_BYTES); use svo_gpu_bucket, which sizes its tables with cudaMalloc",
+                           nb, per_bucket, need * 4, SVO_GPU_BUCKET_STATIC_BYTES);
+    if ((n_in > 0 && !on_device(xy_in_dev)) || (ages_in_dev_or_null && !on_device(ages_in_dev_or_null)) ||
+        (capacity > 0 && (!on_device(xy_out_dev) || !on_device(ages_out_dev))))
+        return static_fail(eb, el, SVO_GPU_E_ARG, "svo_gpu_bucket_static: the point / age arrays must be device memory");
+
+    // ---- set-up, once per device: where the static array lives on the device that is current now
+    int dev = -1;
+    cudaError_t ce = cudaGetDevice(&dev);
+    if (ce != cudaSuccess) return static_fail(eb, el, SVO_GPU_E_CUDA, "cudaGetDevice: %s", cudaGetErrorString(ce));
+    if (dev < 0 || dev >= kStaticMaxDevices) return static_fail(eb, el, SVO_GPU_E_ARG, "device ordinal %d not supported", dev);
+    int* base = g_bucket_static_dev[dev].load(std::memory_order_acquire);
+    if (!base) {
+        ce = cudaGetSymbolAddress((void**)&base, g_bucket_static);
+        if (ce != cudaSuccess || !base)
+            return static_fail(eb, el, SVO_GPU_E_CUDA, "cudaGetSymbolAddress(static bucket scratch) on device %d: %s", dev,
+                               cudaGetErrorString(ce));
+        g_bucket_static_dev[dev].store(base, std::memory_order_release);   // every thread would store the same address
+    }
+
+    cudaStream_t st = (cudaStream_t)stream;
+    BucketBufs bb{};
+    bb.err_flag = base + 1;
+    bb.cell_cnt = base + kStaticHead;
+    bb.cell_last = bb.cell_cnt + nb;
+    bb.cell_slots = bb.cell_last + nb;
+    bb.cells_cap = (size_t)nb;                       // exactly this call's table: the clear kernel touches nothing else
+    bb.slots_cap = (size_t)nb * (size_t)per_bucket;
+    bb.out_xy = reinterpret_cast<float2*>(xy_out_dev);
+    bb.out_age = ages_out_dev;
+    bb.out_count = base;
+    bb.out_cap = capacity;
+    bb.mode = 1;
+
+    // The array still holds whatever the previous call (any thread, any stream) left there: everything this call reads is
+    // rewritten first, in stream order -- the list-length word by the memset, the tables and the error flag by the clear
+    // kernel, the output length by the emit kernel.
+    ce = cudaMemsetAsync(base + 2, 0x7f, sizeof(int), st);   // 0x7f7f7f7f: "as many points as n_in says"
+    if (ce != cudaSuccess) return static_fail(eb, el, SVO_GPU_E_CUDA, "cudaMemsetAsync: %s", cudaGetErrorString(ce));
+    {
+        const size_t n = bb.slots_cap;
+        const int blocks = (int)std::min<size_t>((n + 1023) / 1024, 1184);
+        bucket_clear_kernel<<<std::max(blocks, 1), 256, 0, st>>>(bb, 1);
+    }
+    int nblk = (n_in + 255) / 256;
+    nblk = nblk < 1 ? 1 : (nblk > 592 ? 592 : nblk);
+    bucket_insert_kernel<<<dim3(nblk, 1), 256, 0, st>>>(reinterpret_cast<const float2*>(xy_in_dev), 0, base + 2, n_in, (int)Wc,
+                                                        (int)nb, bucket_size, per_bucket, bb);
+    bucket_emit_kernel<<<dim3((unsigned)((nb + 255) / 256), 1), 256, 0, st>>>(reinterpret_cast<const float2*>(xy_in_dev),
+                                                                              ages_in_dev_or_null, 0, (int)Wc, (int)nb,
+                                                                              per_bucket, bb);
+    ce = cudaGetLastError();
+    if (ce != cudaSuccess) return static_fail(eb, el, SVO_GPU_E_CUDA, "bucket kernels: %s", cudaGetErrorString(ce));
+    int head[2] = {0, 0};   // output length, error flag: two words to the caller's stack, no staging buffer of ours
+    ce = cudaMemcpyAsync(head, base, sizeof(head), cudaMemcpyDeviceToHost, st);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(st);
+    if (ce != cudaSuccess) return static_fail(eb, el, SVO_GPU_E_CUDA, "svo_gpu_bucket_static: %s", cudaGetErrorString(ce));
+    if (head[1])
+        return static_fail(eb, el, SVO_GPU_E_ARG, "a point maps outside the bucket table (undefined behaviour in the reference)");
+    *n_out = head[0];
+    if (head[0] > capacity)
+        return static_fail(eb, el, SVO_GPU_E_CAPACITY, "%d bucketed features exceed the capacity %d", head[0], capacity);
+    return SVO_GPU_OK;
+}
