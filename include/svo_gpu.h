@@ -111,6 +111,10 @@ SVO_GPU_API int svo_gpu_build_pyramid(svo_gpu_ctx* ctx, int slot, int win_w, int
 SVO_GPU_API int svo_gpu_pyramid_levels(int w, int h, int win_w, int win_h, int max_level);
 SVO_GPU_API int svo_gpu_pyramid_margin(int win_w, int win_h);
 SVO_GPU_API int svo_gpu_slot_pyramid(const svo_gpu_ctx* ctx, int slot, int* levels_out, int* margin_out);
+/* How many images `slot` has received so far (every upload call and every svo_gpu_step ingest into it counts).  A caller that
+ * remembers "slot s holds frame F" -- the wrappers' frame cache -- records this number with the tag and treats a different
+ * number as "someone else has written the slot since": the context is reachable by other code (svo::defaultContext()). */
+SVO_GPU_API int svo_gpu_slot_generation(const svo_gpu_ctx* ctx, int slot, unsigned long long* generation_out);
 /* Test/debug read-back of one pyramid level of lane `lane` (tightly packed w*h bytes). */
 SVO_GPU_API int svo_gpu_download_level(svo_gpu_ctx* ctx, int slot, int lane, int level, uint8_t* host, int capacity_bytes,
                                        int* w_out, int* h_out);

@@ -42,6 +42,7 @@ SYMBOLS = {
     "svo_gpu_pyramid_levels": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
     "svo_gpu_pyramid_margin": (C.c_int, [C.c_int, C.c_int]),
     "svo_gpu_slot_pyramid": (C.c_int, [C.c_void_p, C.c_int, _i32p, _i32p]),
+    "svo_gpu_slot_generation": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_ulonglong)]),
     "svo_gpu_download_level": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, _i32p, _i32p]),
     "svo_gpu_download_level_padded": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, _i32p, _i32p,
                                                 _i32p]),

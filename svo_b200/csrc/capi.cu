@@ -27,6 +27,7 @@ struct Slot {
     size_t raw_pitch = 0, raw_lane = 0;
     int w = 0, h = 0, batch = 0;
     bool uploaded = false;
+    unsigned long long gen = 0;     // counts the images this slot has received (any upload path, the step's ingest included)
     DevBuf pyr;
     PyrGeom g{};
     bool pyr_built = false;
@@ -52,11 +53,15 @@ struct StepGraph {
     svo_gpu_step_outputs out{};
     bool has_out = false;
     int batch = 0, kernels = 0, eff = 0, kp_cap = 0;
+    unsigned long long alloc_epoch = 0;   // ctx->alloc_epoch at capture: a graph holds device addresses by value
     const void* pyr_prev = nullptr;
     const void* pyr_cur = nullptr;
 };
 
 constexpr int kStepBase = SVO_GPU_NUM_SLOTS - 3;   // svo_gpu_step's ring of three slots
+// No event orders the next frame's copy / pyramid build after the kernels of steps still in flight: the ring alone makes it
+// safe, because the free slot's last reader belongs to a step that has been waited for.  That needs more slots than steps.
+static_assert(SVO_GPU_STEP_DEPTH + 1 <= 3, "the step's slot ring must be larger than the number of outstanding steps");
 
 thread_local char g_create_error[512] = "";
 
@@ -108,6 +113,7 @@ struct svo_gpu_ctx {
 
     // svo_gpu_step state
     bool step_has_prev = false;
+    unsigned long long alloc_epoch = 0;   // bumped whenever ensure() replaces a device buffer
     int step_cur = kStepBase;
     svo_gpu_step_params step_params{};
     int step_batch = 0;
@@ -124,7 +130,8 @@ struct svo_gpu_ctx {
     // detection beside tracking: FAST and bucketing run on aux_st while the LK kernel runs on st (small batches, see capi_step.inc)
     cudaStream_t aux_st = nullptr;
     // the step builds the new frame's pyramid on pyr_st (highest priority): with a step still in flight it runs beside that
-    // step's FAST and bucketing, as soon as that step's LK no longer needs the slot's previous pyramid
+    // step's kernels without waiting for any of them -- it writes the ring's free slot, which no step in flight reads
+    // (three slots, at most SVO_GPU_STEP_DEPTH = 2 steps outstanding; see the static_assert at kStepBase)
     cudaStream_t pyr_st = nullptr;
     cudaEvent_t ev_pyr = nullptr;
     int pyr_async = 1;      // SVO_GPU_STEP_PYR_ASYNC (0 = pyramid on the main stream)
@@ -183,6 +190,7 @@ int ensure(svo_gpu_ctx* ctx, DevBuf& b, size_t bytes)
 {
     if (bytes <= b.bytes) return 0;
     CK(cudaStreamSynchronize(ctx->st));
+    ++ctx->alloc_epoch;   // captured step graphs hold the old address (bucket tables, mask ...): they must be recorded again
     if (b.p) CK(cudaFree(b.p));
     b.p = nullptr;
     b.bytes = 0;
@@ -473,6 +481,7 @@ static int upload_to_slot(svo_gpu_ctx* ctx, int slot, const uint8_t* images, int
     }
     s.w = w; s.h = h; s.batch = batch;
     s.uploaded = true;
+    ++s.gen;
     s.pyr_built = false;
     return 0;
 }
@@ -530,6 +539,7 @@ extern "C" int svo_gpu_upload_bgr_batch(svo_gpu_ctx* ctx, int slot, const uint8_
     s.raw_pitch = pitch; s.raw_lane = lane;
     s.w = w; s.h = h; s.batch = batch;
     s.uploaded = true;
+    ++s.gen;
     s.pyr_built = false;
     return 0;
 }
@@ -606,6 +616,13 @@ extern "C" int svo_gpu_slot_pyramid(const svo_gpu_ctx* ctx, int slot, int* level
     const Slot& s = ctx->slots[slot];
     if (levels_out) *levels_out = s.pyr_built ? s.g.nlevels : 0;
     if (margin_out) *margin_out = s.pyr_built ? s.g.P : 0;
+    return 0;
+}
+
+extern "C" int svo_gpu_slot_generation(const svo_gpu_ctx* ctx, int slot, unsigned long long* generation_out)
+{
+    if (!ctx || slot < 0 || slot >= SVO_GPU_NUM_SLOTS || !generation_out) return SVO_GPU_E_ARG;
+    *generation_out = ctx->slots[slot].gen;
     return 0;
 }
 

@@ -23,6 +23,7 @@ struct SlotTag {
     bool valid = false;
     int rows = 0, cols = 0, type = 0;
     uint64_t sum = 0;
+    unsigned long long gen = 0;   // svo_gpu_slot_generation right after OUR upload: anyone else's upload into the slot changes it
     uint64_t used = 0;     // LRU stamp
 };
 
@@ -113,6 +114,13 @@ int slot_of(CtxEntry& e, const cv::Mat& m, int keep = -1)
         for (int s = 0; s < SVO_GPU_NUM_SLOTS; ++s) {
             SlotTag& t = e.slot[s];
             if (t.valid && s != keep && t.rows == m.rows && t.cols == m.cols && t.type == m.type() && t.sum == sum) {
+                // the context is public (svo::defaultContext()): a direct svo_gpu_upload / svo_gpu_step on it may have
+                // replaced the slot's image behind the tag's back
+                unsigned long long gen = 0;
+                if (svo_gpu_slot_generation(e.ctx, s, &gen) != SVO_GPU_OK || gen != t.gen) {
+                    t.valid = false;
+                    continue;
+                }
                 t.used = ++e.tick;
                 ++e.stats.hits;
                 return s;
@@ -130,6 +138,7 @@ int slot_of(CtxEntry& e, const cv::Mat& m, int keep = -1)
     SlotTag& t = e.slot[victim];
     t.valid = g_tab.cache;
     t.rows = m.rows; t.cols = m.cols; t.type = m.type(); t.sum = sum; t.used = ++e.tick;
+    svo_gpu_slot_generation(e.ctx, victim, &t.gen);
     ++e.stats.uploads;
     return victim;
 }

@@ -163,6 +163,41 @@ int main(int argc, char** argv)
         fprintf(stderr, "detect() returned without a GPU: a CPU fallback must not exist\n");
         return 1;
     }
+    if (argc == 2 && !strcmp(argv[1], "--stale-slot")) {
+        // The wrappers remember which frame each slot of the thread's context holds; the context itself is public
+        // (svo::defaultContext()).  Someone who uploads into its slots directly must not make the wrappers compute on the
+        // wrong pixels: a cached frame whose slot has been overwritten is uploaded again.
+        const int w = 160, h = 120;
+        cv::Mat a(cv::Size(w, h), CV_8UC1, 0), b(cv::Size(w, h), CV_8UC1, 0);
+        unsigned x = 12345u, y = 777u;
+        for (int r = 0; r < h; ++r)
+            for (int c = 0; c < w; ++c) {
+                x = x * 1664525u + 1013904223u;
+                y = y * 22695477u + 1u;
+                a.data[r * a.step + c] = (unsigned char)(y >> 24);   // two different noise images: FAST finds many corners in each
+                b.data[r * b.step + c] = (unsigned char)(x >> 24);
+            }
+        auto det = svo::GpuFastDetector::create(20, true);
+        std::vector<cv::KeyPoint> k0, k1, kb;
+        det->detect(a, k0);
+        det->detect(b, kb);
+        svo_gpu_ctx* ctx = svo::defaultContext(svo::currentDevice());
+        for (int s = 0; s < SVO_GPU_NUM_SLOTS; ++s)       // overwrite every slot behind the wrappers' back
+            if (svo_gpu_upload(ctx, s, b.data, w, h, b.step) != SVO_GPU_OK) { fprintf(stderr, "upload failed\n"); return 1; }
+        const svo::FrameCacheStats c0 = svo::frameCacheStats();
+        det->detect(a, k1);
+        const svo::FrameCacheStats c1 = svo::frameCacheStats();
+        auto equal = [](const std::vector<cv::KeyPoint>& p, const std::vector<cv::KeyPoint>& q) {
+            if (p.size() != q.size()) return false;
+            for (size_t i = 0; i < p.size(); ++i)
+                if (p[i].pt.x != q[i].pt.x || p[i].pt.y != q[i].pt.y || p[i].response != q[i].response) return false;
+            return true;
+        };
+        const bool same = !k0.empty() && equal(k0, k1) && !equal(k0, kb);
+        printf("stale-slot: %zu keypoints before, %zu after, %zu on the other frame, uploads +%lld hits +%lld -> %s\n", k0.size(),
+               k1.size(), kb.size(), c1.uploads - c0.uploads, c1.hits - c0.hits, same && c1.uploads - c0.uploads == 1 ? "ok" : "FAILED");
+        return same && c1.uploads - c0.uploads == 1 ? 0 : 1;
+    }
     if ((argc == 4 || argc == 5) && !strcmp(argv[1], "--batch")) {
         // optional 4th argument: features_to_track -> the reference's own track policy (FrontendParams::carryTracks); each
         // stream's record then ends with its key-frame flag and its survivor indices

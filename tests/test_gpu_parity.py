@@ -308,3 +308,26 @@ def test_klt_unsupported_and_state(ctx, c1_frames):
     with pytest.raises(capi.SvoGpuError) as e:
         ctx.klt(0, 1, pts, win=(41, 41))              # pyramids were built for a smaller window
     assert e.value.code == capi.E_STATE
+
+
+def test_klt_refuses_pyramids_shallower_than_max_level(ctx, small_frames):
+    """cv::calcOpticalFlowPyrLK(maxLevel = 3) on a 320x240 frame uses levels 0..3.  Pyramids built with maxLevel 1 hold two:
+    running LK on them would return different tracks than OpenCV with SVO_GPU_OK, so the direct C-ABI calls refuse
+    (the C++ wrappers rebuild the pyramid instead, svo_b200/host/feature.cpp:need_pyramid)."""
+    a, b = small_frames
+    ctx.upload(0, a)
+    ctx.upload(1, b)
+    ctx.build_pyramid(0, (21, 21), 1)
+    ctx.build_pyramid(1, (21, 21), 1)
+    pts = np.array([[100.0, 100.0], [50.5, 60.25]], np.float32)
+    ctx.klt(0, 1, pts, win=(21, 21), max_level=1, max_count=30, epsilon=0.01)          # what the slots hold: fine
+    for call in (lambda: ctx.klt(0, 1, pts, win=(21, 21), max_level=3, max_count=30, epsilon=0.01),
+                 lambda: ctx.track_frames(0, 1, pts, win=(21, 21), max_level=3)):
+        with pytest.raises(capi.SvoGpuError) as e:
+            call()
+        assert e.value.code == capi.E_STATE and "levels" in str(e.value)
+    ctx.build_pyramid(0, (21, 21), 3)
+    ctx.build_pyramid(1, (21, 21), 3)
+    ctx.klt(0, 1, pts, win=(21, 21), max_level=3, max_count=30, epsilon=0.01)
+    # asking for more levels than the image supports is not an error: OpenCV stops at the same level
+    ctx.klt(0, 1, pts, win=(21, 21), max_level=4, max_count=30, epsilon=0.01)

@@ -220,3 +220,13 @@ def test_sequence_batch_reference_track_policy(exe, oracle, tmp_path):
             assert np.array_equal(feats, ref["bucket_xy"]) and np.array_equal(surv, ref.get("survivor_index", np.zeros(0, np.int32))), (t, s)
             kfs.append(kf)
     assert any(k == 0 for k in kfs[S:]) and any(k == 1 for k in kfs[S:])
+
+
+@pytest.mark.gpu
+def test_frame_cache_notices_foreign_uploads(exe):
+    """The wrappers' frame cache tags slots of a context that svo::defaultContext() also hands to the caller.  After direct
+    svo_gpu_upload calls into those slots, detect() on a frame the cache "knew" must upload it again (slot generation
+    counter, svo_gpu_slot_generation) and return that frame's keypoints, not the foreign image's."""
+    r = subprocess.run([exe, "--stale-slot"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "-> ok" in r.stdout

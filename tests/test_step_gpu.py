@@ -141,8 +141,9 @@ def test_step_pipelined_ingest(oracle):
 def test_step_submit_wait(oracle, mem, graph, monkeypatch):
     """svo_gpu_step_submit / svo_gpu_step_wait with two steps outstanding (submit(t + 1) before wait(t)): each step's
     results, read after ITS wait, equal the synchronous CPU pipeline; host frames are prefetched one step ahead.
-    SVO_GPU_STEP_GRAPH=1: from the third step on the chain LK .. counts is a captured CUDA graph, replayed per step (its
-    ev_klt an external event-record node the next step's pyramid build waits for); 0: every step enqueued call by call."""
+    SVO_GPU_STEP_GRAPH=1: from the third step on the chain LK .. counts is a captured CUDA graph, replayed per step (the next
+    step's pyramid build waits for none of it: it writes the free slot of the three-slot ring); 0: every step enqueued call
+    by call."""
     import torch
     from oracle.cpu_pipeline import CpuFrontend
     monkeypatch.setenv("SVO_GPU_STEP_GRAPH", graph)
@@ -269,3 +270,28 @@ def test_step_with_pageable_outputs(oracle, monkeypatch):
                 _check_lane(fe, b, cpus[b].step(seqs[b, done]), first=(done == 0))
             done += 1
         assert done == T
+
+
+def test_step_graph_survives_bucket_table_regrowth(oracle, monkeypatch):
+    """A captured step graph holds the bucket tables' addresses by value.  svo_gpu_bucket with a finer grid on the same
+    context frees and re-allocates those tables; the next step must record its graph again (allocation epoch in the graph
+    key) instead of replaying one that writes freed memory.  SVO_GPU_BUCKET_MODE=1 keeps the step on the three
+    global-memory kernels, the only path that uses the tables."""
+    from oracle.cpu_pipeline import CpuFrontend
+    monkeypatch.setenv("SVO_GPU_BUCKET_MODE", "1")
+    monkeypatch.setenv("SVO_GPU_STEP_GRAPH", "1")
+    seqs = _seqs(10)
+    B = seqs.shape[0]
+    rng = np.random.default_rng(12)
+    pts = rng.uniform([0, 0], [W, H], (3000, 2)).astype(np.float32)
+    with capi.Context(max_w=W, max_h=H, max_levels=4, max_points=8192, max_batch=B) as ctx:
+        fe = Frontend(ctx, W, H, B, kp_capacity=8192, bucket_capacity=2048, max_tracks=400, mask_half=10.0)
+        cpus = [CpuFrontend(fe.pdict, impl="orc") for _ in range(B)]
+        for t in range(seqs.shape[1]):
+            if t == 6:                                   # graphs of all slots are recorded by now; grow the tables under them
+                gx, ga = ctx.bucket(pts, np.zeros(len(pts), np.int32), W, H, 3, 6)
+                ox, oa = oracle.orc_bucket(pts, np.zeros(len(pts), np.int32), W, H, 3, 6)
+                assert np.array_equal(gx, ox) and np.array_equal(ga, oa)
+            fe.step_host(np.ascontiguousarray(seqs[:, t]))
+            for b in range(B):
+                _check_lane(fe, b, cpus[b].step(seqs[b, t]), first=(t == 0))
