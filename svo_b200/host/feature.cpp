@@ -23,6 +23,9 @@ struct SlotTag {
     bool valid = false;
     int rows = 0, cols = 0, type = 0;
     uint64_t sum = 0;
+    // second key: the first and last (up to) 64 bytes of the frame, compared verbatim on a checksum match -- the checksum is
+    // not cryptographic, and a collision would track against a stale pyramid without any sign of it
+    unsigned char head[64] = {}, tail[64] = {};
     unsigned long long gen = 0;   // svo_gpu_slot_generation right after OUR upload: anyone else's upload into the slot changes it
     uint64_t used = 0;     // LRU stamp
 };
@@ -105,6 +108,12 @@ uint64_t image_checksum(const cv::Mat& m)
     return h;
 }
 
+size_t edge_bytes(const cv::Mat& m) { return std::min<size_t>(64, (size_t)m.cols * m.elemSize()); }
+const unsigned char* last_row_tail(const cv::Mat& m)
+{
+    return m.data + (size_t)(m.rows - 1) * m.step + (size_t)m.cols * m.elemSize() - edge_bytes(m);
+}
+
 // The slot of the thread's context that holds `m` (uploading it, into the least recently used slot other than `keep`, if no
 // slot does).  Every image argument of the wrappers goes through here.
 int slot_of(CtxEntry& e, const cv::Mat& m, int keep = -1)
@@ -113,7 +122,8 @@ int slot_of(CtxEntry& e, const cv::Mat& m, int keep = -1)
     if (g_tab.cache)
         for (int s = 0; s < SVO_GPU_NUM_SLOTS; ++s) {
             SlotTag& t = e.slot[s];
-            if (t.valid && s != keep && t.rows == m.rows && t.cols == m.cols && t.type == m.type() && t.sum == sum) {
+            if (t.valid && s != keep && t.rows == m.rows && t.cols == m.cols && t.type == m.type() && t.sum == sum &&
+                memcmp(t.head, m.data, edge_bytes(m)) == 0 && memcmp(t.tail, last_row_tail(m), edge_bytes(m)) == 0) {
                 // the context is public (svo::defaultContext()): a direct svo_gpu_upload / svo_gpu_step on it may have
                 // replaced the slot's image behind the tag's back
                 unsigned long long gen = 0;
@@ -139,6 +149,8 @@ int slot_of(CtxEntry& e, const cv::Mat& m, int keep = -1)
     t.valid = g_tab.cache;
     t.rows = m.rows; t.cols = m.cols; t.type = m.type(); t.sum = sum; t.used = ++e.tick;
     svo_gpu_slot_generation(e.ctx, victim, &t.gen);
+    memcpy(t.head, m.data, edge_bytes(m));
+    memcpy(t.tail, last_row_tail(m), edge_bytes(m));
     ++e.stats.uploads;
     return victim;
 }
