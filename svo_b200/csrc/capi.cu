@@ -108,6 +108,7 @@ struct svo_gpu_ctx {
     int* h_small = nullptr;       // 6 * max_batch + 16 ints
     int fetch_hint = 0;           // keypoints svo_gpu_fast last returned (+ 25 %): copied back together with the count
     int bucket_fetch_hint = 0;    // same for svo_gpu_bucket
+    uint8_t* h_klt = nullptr;     // pinned staging of svo_gpu_klt's results (13 bytes per point + the iteration count), allocated by its first call
     uint8_t* h_bucket = nullptr;  // pinned staging of svo_gpu_bucket's speculative read-back (bucket_stage_cap entries)
     int bucket_stage_cap = 0;
 
@@ -417,6 +418,7 @@ extern "C" int svo_gpu_destroy(svo_gpu_ctx* ctx)
     for (void* p : bufs) cudaFree(p);
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
     if (ctx->h_bucket) cudaFreeHost(ctx->h_bucket);
+    if (ctx->h_klt) cudaFreeHost(ctx->h_klt);
     if (ctx->st) cudaStreamDestroy(ctx->st);
     delete ctx;
     return 0;
