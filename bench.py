@@ -493,6 +493,49 @@ def run_b200(args):
     ctx.step_profile(False)
     clocks = sampler.stop(t_start, t_stop) if sampler else None
     stage, iters = acc["stage"], acc["iters"]
+
+    # ---- config 5 as BASELINE.json words it: `--streams` sequences IN TOTAL, sharded over the ranks (strong split), measured
+    #      by the same ranks right after the weak loops so that the driver's scaling run carries both.  Same step, same frames
+    #      (the first len(ids) lanes of this rank's ring), a context of its own; outside the timed regions above.
+    strong = None
+    if world > 1 and not args.total_streams and not args.no_extras:
+        tot = args.streams
+        Ss = len(sharding.sequences_of(rank, world, tot))
+        ctx_s = capi.Context(device=local, max_w=w, max_h=h, max_levels=levels, max_points=max(32768, w * h // 16), max_batch=Ss)
+        fe_s = Frontend(ctx_s, w, h, Ss, bucket_capacity=cells, **step_params(wl))
+        st_s = torch.cuda.ExternalStream(ctx_s.stream)
+        es = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+
+        def loop_s(i0, i1, submit):
+            for i in range(i0, i1):
+                submit(i)
+                if fe_s.outstanding == 2:
+                    fe_s.wait()
+            while fe_s.outstanding:
+                fe_s.wait()
+
+        def sub_h(i):
+            fe_s.submit(hptr(i), hptr(i + 1), capi.MEM_HOST, w, w * h)
+
+        def sub_d(i):
+            fe_s.submit(dev[i % RING].data_ptr(), None, capi.MEM_DEVICE, pitch, h * pitch, with_outputs=False)
+
+        strong = {"total_streams": tot, "streams_this_rank": Ss, "scaling": "strong", "steps": K, "warmup": WU}
+        for key, sub in (("e2e", sub_h), ("value", sub_d)):
+            fe_s.reset()
+            loop_s(0, WU, sub)
+            barrier()
+            es[0].record(st_s)
+            loop_s(WU, WU + K, sub)
+            es[1].record(st_s)
+            barrier()
+            ms = max_over_ranks(es[0].elapsed_time(es[1]))
+            strong[key] = tot * K / (ms * 1e-3)
+            strong[key + "_ms_per_step"] = ms / K
+        strong["unit"] = "frames/s"
+        strong["note"] = ("%d sequences in total over %d GPUs; compare with the N = 1 line of the weak run, which is the same "
+                          "%d sequences on one GPU" % (tot, world, tot))
+        ctx_s.close()
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -574,6 +617,8 @@ def run_b200(args):
         "stats": {"keypoints_per_frame": kp, "bucketed_per_frame": bk, "tracks_per_frame": n_trk,
                   "status_ok_frac": ok_sum / max(trk_sum, 1), "streams_this_rank": S},
     }
+    if strong:
+        line["strong"] = strong
     line["klt_tracks_per_s"] = total_streams * n_trk * K / (dev_ms * 1e-3)
     # stage-only rates (KLT-only and FAST-only reported next to the whole front-end), this rank's launches
     line["stage_rates"] = {
