@@ -24,6 +24,8 @@
 //     loads and forms Ix, Iy separably.  Windows that touch the image border (where OpenCV's derivative image is
 //     ZERO-padded, which breaks that identity) take the literal path: Scharr plane with zeros outside, then bilinear.
 //   - lanes never diverge: every per-feature scalar is warp-uniform; reductions are REDUX on 16-bit halves (exact).
+#include <stdio.h>
+
 #include <algorithm>
 #include <type_traits>
 
@@ -185,6 +187,34 @@ __device__ __forceinline__ int run_px(const RunRow& top, const RunRow& bot, uint
     return dp2a_lo_su(wb, b, dp2a_lo_su(wt, t, c));
 }
 
+// Checked build (make EXTRA=-DSVO_BOUNDS_CHECK, see profiles/r03_bounds_check.txt): the two staging routines below read
+// without predicates and rely on the margin arithmetic of DESIGN.md section 3.  In the checked build every one of those reads
+// is tested against the padded extent of its pyramid level -- rows [-P, h + P), columns [-P, w + P) around the interior --
+// which is tighter than the allocation: a read outside it would be memory-safe at best and would see bytes that are not the
+// BORDER_REFLECT_101 margin.  A violation prints the site and traps (the call returns SVO_GPU_E_CUDA).
+#ifdef SVO_BOUNDS_CHECK
+#ifndef SVO_BOUNDS_CHECK_SHRINK
+#define SVO_BOUNDS_CHECK_SHRINK 0   // > 0: pretend the margin is that much narrower -- the control run that shows the check fires
+#endif
+__device__ __noinline__ void check_level_read(const uint8_t* p, int bytes, const uint8_t* origin, int w, int h, int pitch, int P,
+                                              int site)
+{
+    const long long d = p - origin;   // byte offset from interior pixel (0, 0)
+    long long row = d / pitch, col = d - row * pitch;
+    if (col < -P) { col += pitch; --row; }
+    else if (col >= pitch - P) { col -= pitch; ++row; }
+    if (row < -P || row >= h + P || col < -P || col + bytes > w + P) {
+        printf("SVO_BOUNDS_CHECK site %d: rows %lld cols %lld..%lld outside [-%d, %d) x [-%d, %d)\n", site, row, col, col + bytes,
+               P, h + P, P, w + P);
+        __trap();
+    }
+}
+#define SVO_CHECK_READ(p, bytes, origin, L, P, site) \
+    check_level_read((p), (bytes), (origin), (L).w, (L).h, (L).pitch, (P) - SVO_BOUNDS_CHECK_SHRINK, (site))
+#else
+#define SVO_CHECK_READ(p, bytes, origin, L, P, site) ((void)0)
+#endif
+
 // Stages rows of RP bytes whose first byte is column x0 of row y0 (any alignment) into shared memory, rows RP bytes
 // apart: two aligned 32-bit loads + one funnel shift per output word, all loads issued before the first store.
 // Works in PASSES whole passes of 32 / (RP/4) rows, so ROWS is rounded up (the pyramid margin covers the extra rows) and
@@ -309,8 +339,10 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) klt_run_kernel(const KltArgs
             sy0 = iny - G::MJ;
             const uint8_t* src = Jorigin + (long long)(sy0 + sJ_r) * L.pitch + (sx0 + 4 * sJ_c);
 #pragma unroll
-            for (int k = 0; k < G::PASSJ; ++k)
+            for (int k = 0; k < G::PASSJ; ++k) {
+                SVO_CHECK_READ(src + (long long)(k * G::RPPJ) * L.pitch, 4, Jorigin, L, a.g.P, 2);
                 cp_async4(sJ_dst + k * G::RPPJ * G::PJ, src + (long long)(k * G::RPPJ) * L.pitch);
+            }
             jstaged = true;
             rsafe = sx0 >= -WW && sx0 + G::DXMAX < L.w && sy0 >= -WH && sy0 + G::DYMAX < L.h;
         };
@@ -325,6 +357,12 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) klt_run_kernel(const KltArgs
         {
             const int x0 = ipx - 1;
             const uint8_t* src0 = Ppyr + L.off + (long long)(ipy - 1 + sI_r) * L.pitch + ((x0 & ~3) + 4 * sI_c);
+#ifdef SVO_BOUNDS_CHECK
+            {
+                constexpr int RPPI = 32 / (G::RPI / 4), PASSI = (G::IROWS + RPPI - 1) / RPPI;   // as in stage_shifted
+                for (int k = 0; k < PASSI; ++k) SVO_CHECK_READ(src0 + (long long)(k * RPPI) * L.pitch, 8, Ppyr + L.off, L, a.g.P, 1);
+            }
+#endif
             stage_shifted<G::IROWS, G::RPI>(sI_dst, src0, L.pitch, x0);
         }
         __syncwarp();
